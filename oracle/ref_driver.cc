@@ -1,0 +1,272 @@
+// TEST INFRASTRUCTURE -- not a product path (see oracle/README.md).
+//
+// Driver around the REFERENCE's own translation units, compiled where they lie
+// under /root/reference by oracle/Makefile (never copied into this repo):
+//   gpu-simulator/trace-parser/trace_parser.cc      (text -> inst_trace_t)
+//   gpu-simulator/trace-driven/trace_driven.cc      (inst_trace_t -> trace_warp_inst_t)
+//   gpu-simulator/gpgpu-sim/src/abstract_hardware_model.cc (generate_mem_accesses)
+// It replays what the timing model does per instruction -- parse_from_trace_struct
+// (trace_driven.cc:57-68), issue() (shader.cc:1030-1117), func_exec_inst ->
+// generate_mem_accesses (trace_driven.cc:608-630) -- and writes every field in the
+// C-ABI record layouts (oracle/dump_format.h).  Counter increments cannot be linked
+// (shader.cc needs the whole simulator) and come from oracle/counters_restate.h.
+//
+//   ref_oracle dump  <kernel.traceg> <out.tidump> [cfg.bin]
+//   ref_oracle time  <kernel.traceg> [cfg.bin] [parse|convert|coalesce]
+//
+// Local-space instructions are decoded but not coalesced: the reference rewrites
+// their addresses per SM at issue time (trace_driven.cc:593-601), which is outside
+// the trace-only path.
+
+#include <bits/stdc++.h>
+
+#include "../ISA_Def/ampere_opcode.h"
+#include "../ISA_Def/kepler_opcode.h"
+#include "../ISA_Def/pascal_opcode.h"
+#include "../ISA_Def/trace_opcode.h"
+#include "../ISA_Def/turing_opcode.h"
+#include "../ISA_Def/volta_opcode.h"
+#include "abstract_hardware_model.h"
+#include "gpgpu_context.h"
+#include "option_parser.h"
+#include "trace_driven.h"
+
+#include "counters_restate.h"
+#include "dump_format.h"
+#include "qv100_cfg.h"
+
+// ---- option registry stub: trace_config::reg_options hands us its char* slots
+static std::map<std::string, char **> g_cstr_opts;
+void option_parser_register(option_parser_t, const char *name, enum option_dtype type,
+                            void *variable, const char *, const char *defaultvalue) {
+  if (type == OPT_CSTR) {
+    *(char **)variable = strdup(defaultvalue);
+    g_cstr_opts[name] = (char **)variable;
+  }
+}
+static void set_opt(const char *name, unsigned a, unsigned b) {
+  char buf[64];
+  snprintf(buf, sizeof buf, "%u,%u", a, b);
+  auto it = g_cstr_opts.find(name);
+  if (it == g_cstr_opts.end()) { fprintf(stderr, "no option %s\n", name); exit(2); }
+  *it->second = strdup(buf);
+}
+
+// ---- stats sinks the coalescer calls (abstract_hardware_model.cc:417,469)
+void ptx_stats::ptx_file_line_stats_add_latency(unsigned, unsigned) {}
+void ptx_stats::ptx_file_line_stats_add_smem_bank_conflict(unsigned, unsigned) {}
+void ptx_stats::ptx_file_line_stats_add_uncoalesced_gmem(unsigned, unsigned) {}
+void ptx_stats::ptx_file_line_stats_add_warp_divergence(unsigned, unsigned) {}
+
+struct probe_core_config : public core_config {
+  probe_core_config(gpgpu_context *c) : core_config(c) {}
+  void init() {}
+};
+
+struct probe_inst : public trace_warp_inst_t {
+  probe_inst(const core_config *c) : trace_warp_inst_t(c) {}
+  unsigned shmem_cycles() const { return cycles; }
+};
+
+static const std::unordered_map<std::string, OpcodeChar> *pick_isa(unsigned v) {
+  switch (v) {
+    case 80: case 86: return &Ampere_OpcodeMap;
+    case 70: return &Volta_OpcodeMap;
+    case 60: case 61: return &Pascal_OpcodeMap;
+    case 35: return &Kepler_OpcodeMap;
+    case 75: return &Turing_OpcodeMap;
+  }
+  return NULL;
+}
+
+static ti_config load_cfg(const char *path) {
+  ti_config cfg;
+  ti_oracle::qv100(&cfg);
+  if (path && *path) {
+    FILE *f = fopen(path, "rb");
+    if (!f || fread(&cfg, sizeof cfg, 1, f) != 1) { fprintf(stderr, "bad cfg %s\n", path); exit(2); }
+    fclose(f);
+  }
+  return cfg;
+}
+
+int main(int argc, char **argv) {
+  if (argc < 3) { fprintf(stderr, "usage: ref_oracle dump|time <traceg> ...\n"); return 2; }
+  std::string mode = argv[1];
+  const char *trace_path = argv[2];
+  const char *out_path = NULL, *cfg_path = NULL;
+  int stages = 3;
+  if (mode == "dump") {
+    if (argc < 4) return 2;
+    out_path = argv[3];
+    if (argc > 4) cfg_path = argv[4];
+  } else {
+    if (argc > 3) cfg_path = argv[3];
+    if (argc > 4) stages = !strcmp(argv[4], "parse") ? 1 : !strcmp(argv[4], "convert") ? 2 : 3;
+  }
+  ti_config cfg = load_cfg(cfg_path);
+
+  // The context is only a bag of uid counters + the stats sink for this path; its
+  // constructor would pull in the PTX front end, so it is zero-filled instead.
+  gpgpu_context *gctx = (gpgpu_context *)calloc(1, sizeof(gpgpu_context));
+  gctx->stats = (ptx_stats *)calloc(1, sizeof(ptx_stats));
+  probe_core_config cc(gctx);
+  cc.warp_size = 32;
+  cc.gpgpu_coalesce_arch = cfg.coalesce_arch;
+  cc.mem_warp_parts = cfg.mem_warp_parts;
+  cc.num_shmem_bank = cfg.num_shmem_bank;
+  cc.shmem_limited_broadcast = cfg.shmem_limited_broadcast != 0;
+  cc.gmem_skip_L1D = cfg.gmem_skip_L1D != 0;
+  cc.gpgpu_cache_texl1_linesize = 128;
+  cc.gpgpu_cache_constl1_linesize = 64;
+
+  trace_config tconfig;
+  tconfig.reg_options(NULL);
+  set_opt("-trace_opcode_latency_initiation_int", cfg.lat_int[0], cfg.lat_int[1]);
+  set_opt("-trace_opcode_latency_initiation_sp", cfg.lat_sp[0], cfg.lat_sp[1]);
+  set_opt("-trace_opcode_latency_initiation_dp", cfg.lat_dp[0], cfg.lat_dp[1]);
+  set_opt("-trace_opcode_latency_initiation_sfu", cfg.lat_sfu[0], cfg.lat_sfu[1]);
+  set_opt("-trace_opcode_latency_initiation_tensor", cfg.lat_tensor[0], cfg.lat_tensor[1]);
+  for (int j = 0; j < 8; ++j) {
+    char nm[80];
+    snprintf(nm, sizeof nm, "-trace_opcode_latency_initiation_spec_op_%d", j + 1);
+    set_opt(nm, cfg.lat_spec[j][0], cfg.lat_spec[j][1]);
+  }
+  tconfig.parse_config();
+
+  // the reference echoes header and per-block lines on std::cout; capture them
+  std::ostringstream echo;
+  std::streambuf *old = std::cout.rdbuf(echo.rdbuf());
+
+  trace_parser parser("unused");
+  auto t0 = std::chrono::steady_clock::now();
+  kernel_trace_t *kinfo = parser.parse_kernel_info(trace_path);
+  const std::unordered_map<std::string, OpcodeChar> *isa = pick_isa(kinfo->binary_verion);
+  if (!isa) {
+    std::cout.rdbuf(old);
+    printf("unsupported binary version: %d\n", kinfo->binary_verion);
+    return 4;
+  }
+  unsigned threads = kinfo->tb_dim_x * kinfo->tb_dim_y * kinfo->tb_dim_z;
+  unsigned n_warps = (threads + 31) / 32;
+  std::vector<std::vector<inst_trace_t>> warps(n_warps);
+  std::vector<std::vector<inst_trace_t> *> ptrs;
+  for (auto &w : warps) ptrs.push_back(&w);
+
+  ti_dump d;
+  ti_oracle::counter_acc acc;
+  d.txn_off.push_back(0);
+  uint64_t n_inst_total = 0, n_txn_total = 0, n_tb_total = 0;
+  const bool dump = mode == "dump";
+
+  for (;;) {
+    echo.str("");
+    parser.get_next_threadblock_traces(ptrs, kinfo->trace_verion, kinfo->ifs);
+    std::string e = echo.str();
+    if (e.empty()) break;  // no "thread block = " line seen: end of file
+    n_tb_total++;
+    ti_tb_rec tb;
+    memset(&tb, 0, sizeof tb);
+    sscanf(e.c_str(), "thread block = %d,%d,%d", &tb.x, &tb.y, &tb.z);
+    tb.first_warp = (uint32_t)d.warp.size();
+    tb.first_inst = (uint32_t)n_inst_total;
+    if (dump) d.tb.push_back(tb);
+    for (unsigned w = 0; w < n_warps; ++w) {
+      if (dump) {
+        ti_warp_rec wr = {w, (uint32_t)warps[w].size(), (uint32_t)n_inst_total, 0};
+        d.warp.push_back(wr);
+      }
+      for (size_t i = 0; i < warps[w].size(); ++i) {
+        const inst_trace_t &t = warps[w][i];
+        n_inst_total++;
+        if (stages < 2) continue;
+        probe_inst inst(&cc);
+        inst.parse_from_trace_struct(t, isa, &tconfig, kinfo);
+        // shader_core_ctx::issue_warp -> warp_inst_t::issue (shader.cc:1030-1117)
+        inst.issue(inst.get_active_mask(), w, 0, w, 0);
+        bool is_local = inst.space.get_type() == local_space;
+        unsigned cycles = 0;
+        if (stages >= 3 && (inst.is_load() || inst.is_store()) && !is_local) {
+          inst.generate_mem_accesses();  // trace_driven.cc:620-622
+          unsigned st = inst.space.get_type();
+          if ((st == shared_space || st == sstarr_space) &&
+              (inst.op == LOAD_OP || inst.op == STORE_OP) && inst.active_count() > 0)
+            cycles = inst.shmem_cycles();
+        }
+        n_txn_total += inst.accessq_count();
+        acc.issue(cfg, inst.op, inst.sp_op, inst.active_count(), inst.latency,
+                  inst.const_cache_operand, inst.space.get_type(), inst.is_store());
+        acc.ints.smem_cycles += cycles;
+        if (!dump) continue;
+
+        ti_inst_rec r;
+        memset(&r, 0, sizeof r);
+        r.pc = t.m_pc;
+        r.mask = t.mask;
+        r.mem_idx = 0xFFFFFFFFu;
+        if (t.reg_dsts_num) r.dst = (uint8_t)t.reg_dest[0];
+        for (unsigned m = 0; m < t.reg_srcs_num; ++m) r.src[m] = (uint8_t)t.reg_src[m];
+        // m_opcode is private; the table gives the same id again
+        r.opcode_id = (uint8_t)isa->find(t.get_opcode_tokens()[0])->second.opcode;
+        r.op = (uint8_t)inst.op;
+        r.pack_a = (uint8_t)((unsigned)inst.sp_op | (((int)inst.oprnd_type + 1) << 5));
+        r.pack_b = (uint8_t)(t.reg_srcs_num | (t.reg_dsts_num << 3) | ((unsigned)inst.memory_op << 4) |
+                             ((inst.isatomic() ? 1 : 0) << 6) | ((inst.const_cache_operand ? 1 : 0) << 7));
+        r.pack_c = (uint8_t)((unsigned)inst.space.get_type() | ((unsigned)inst.cache_op << 4) |
+                             ((t.memadd_info ? 1 : 0) << 7));
+        r.data_size = (uint8_t)inst.data_size;
+        r.cycles = (uint8_t)cycles;
+        r.latency = (uint16_t)inst.latency;
+        r.initiation_interval = (uint8_t)inst.initiation_interval;
+        r.opcode_len = (uint8_t)t.opcode.size();
+        d.opcode_blob += t.opcode;
+        d.opcode_blob.push_back('\0');
+        if (t.memadd_info) {
+          r.mem_idx = (uint32_t)(d.rows.size() / 32);
+          for (int s = 0; s < 32; ++s) d.rows.push_back(t.memadd_info->addrs[s]);
+          // m_accessq is drained from the back by the ld/st unit; keep list order
+          std::vector<ti_txn_rec> q;
+          while (!inst.accessq_empty()) {
+            const mem_access_t &a = inst.accessq_back();
+            ti_txn_rec x;
+            memset(&x, 0, sizeof x);
+            x.addr = a.get_addr();
+            x.lane_mask = (uint32_t)a.get_warp_mask().to_ulong();
+            mem_access_byte_mask_t bm = a.get_byte_mask();
+            for (int b = 0; b < 128; ++b)
+              if (bm.test(b)) x.byte_mask[b >> 5] |= 1u << (b & 31);
+            x.size = (uint8_t)a.get_size();
+            x.sector_mask = (uint8_t)a.get_sector_mask().to_ulong();
+            x.type = (uint8_t)a.get_type();
+            x.is_write = a.is_write() ? 1 : 0;
+            q.push_back(x);
+            inst.accessq_pop_back();
+          }
+          for (size_t k = q.size(); k-- > 0;) d.txn.push_back(q[k]);
+          d.txn_off.push_back((uint32_t)d.txn.size());
+        }
+        d.inst.push_back(r);
+      }
+    }
+    if (kinfo->ifs->eof()) break;
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  std::cout.rdbuf(old);
+  double sec = std::chrono::duration<double>(t1 - t0).count();
+
+  acc.ints.n_inst = n_inst_total;
+  acc.ints.n_tb = n_tb_total;
+  acc.ints.n_txn = n_txn_total;
+  if (dump) {
+    acc.ints.n_mem = d.rows.size() / 32;
+    acc.ints.n_warp = d.warp.size();
+    d.counters = acc.ints;
+    d.power = acc.dbl;
+    if (!ti_dump_write(d, out_path)) { fprintf(stderr, "cannot write %s\n", out_path); return 3; }
+  }
+  printf("{\"impl\":\"reference\",\"stages\":%d,\"seconds\":%.6f,\"n_inst\":%llu,\"n_tb\":%llu,\"n_txn\":%llu}\n",
+         stages, sec, (unsigned long long)n_inst_total, (unsigned long long)n_tb_total,
+         (unsigned long long)n_txn_total);
+  parser.kernel_finalizer(kinfo);
+  return 0;
+}
