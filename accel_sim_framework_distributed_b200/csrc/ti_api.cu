@@ -1,0 +1,456 @@
+// Device half of the C ABI: context, kernel objects, buffers, the launch of the
+// fused decode kernel and the copies either side of it.  There is no CPU fallback:
+// without a CUDA device every compute entry point returns TI_ERR_NO_DEVICE.
+#ifdef TI_EMU
+#include "cuda_runtime_emu.h"
+#else
+#include <cuda_runtime.h>
+#endif
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "ti_internal.h"
+#include "ti_kernels.cuh"
+
+// the merged ISA table (generated from the reference's ISA_Def headers)
+#define TI_ISA_BEGIN static const struct IsaRow { const char *name; uint8_t id[5]; uint8_t cat[5]; } kIsaRows[] = {
+#define TI_ISA_ROW(n, a, b, c, d, e, f, g, h, i, j) {n, {a, b, c, d, e}, {f, g, h, i, j}},
+#define TI_ISA_END };
+#define TI_SPOP_BEGIN static const uint8_t kSpopTable[] = {
+#define TI_SPOP(i, v) v,
+#define TI_SPOP_END };
+#include "isa_tables.inc"
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      ti::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__);   \
+      return TI_ERR_CUDA;                                                                          \
+    }                                                                                              \
+  } while (0)
+
+namespace {
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+  ti_status ensure(size_t need) {
+    if (need <= bytes) return TI_OK;
+    if (p) cudaFree(p);
+    p = nullptr; bytes = 0;
+    CK(cudaMalloc(&p, need));
+    bytes = need;
+    return TI_OK;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+};
+struct HostBuf {
+  void *p = nullptr;
+  size_t bytes = 0;
+  ti_status ensure(size_t need) {
+    if (need <= bytes) return TI_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr; bytes = 0;
+    CK(cudaMallocHost(&p, need ? need : 1));
+    bytes = need;
+    return TI_OK;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
+};
+
+int arch_column(unsigned v) {  // trace_driven.cc:100-118
+  switch (v) {
+    case 35: return 0;
+    case 60: case 61: return 1;
+    case 70: return 2;
+    case 75: return 3;
+    case 80: case 86: return 4;
+  }
+  return -1;
+}
+
+}  // namespace
+
+struct ti_ctx {
+  ti_config cfg;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  ti::IsaSlot *d_isa[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  uint8_t *d_spop = nullptr;
+  int grid = 0;
+};
+
+struct ti_kernel {
+  ti_ctx *ctx = nullptr;
+  ti_kernel_hdr hdr;
+  int col = -1;
+  const char *h_body = nullptr;   // host body (owned pinned file image or borrowed)
+  size_t body_len = 0;
+  HostBuf h_file;                 // owns the file image for ti_kernel_open_file
+  const uint8_t *d_borrowed = nullptr;
+  DevBuf d_text;
+  size_t sh_begin = 0, sh_len = 0;
+  bool uploaded = false, decoded = false, synced = false, retried = false;
+  DevBuf inst, rows, txn_off, txn, tb, warp, state1, state2, globals, counters;
+  uint64_t cap_inst = 0, cap_mem = 0, cap_txn = 0, cap_tb = 0, cap_warp = 0;
+  HostBuf h_inst, h_rows, h_txn_off, h_txn, h_tb, h_warp, h_small;
+  ti_counts counts;
+  ti_counters host_counters;
+  float decode_ms = 0;
+};
+
+static ti_status launch_decode(ti_kernel *k);
+
+extern "C" {
+
+int ti_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+ti_status ti_ctx_create(const ti_config *cfg, ti_ctx **out) {
+  if (!cfg || !out) return TI_ERR_INVALID_ARG;
+  *out = nullptr;
+  if (ti_device_count() <= cfg->device) { ti::set_error("CUDA device %d not present", cfg->device); return TI_ERR_NO_DEVICE; }
+  if (cfg->coalesce_arch < 13) { ti::set_error("coalesce_arch < 13 aborts in the reference (abstract_hardware_model.cc:436)"); return TI_ERR_INVALID_ARG; }
+  const int parts = cfg->mem_warp_parts;
+  if (parts < 1 || parts > 32 || (32 % parts) || cfg->num_shmem_bank < 1) { ti::set_error("bad mem_warp_parts / num_shmem_bank"); return TI_ERR_INVALID_ARG; }
+  const uint32_t *lats[5] = {cfg->lat_int, cfg->lat_sp, cfg->lat_dp, cfg->lat_sfu, cfg->lat_tensor};
+  for (int i = 0; i < 13; ++i) {
+    const uint32_t *l = i < 5 ? lats[i] : cfg->lat_spec[i - 5];
+    if (l[0] > 65535 || l[1] > 255) { ti::set_error("latency > 65535 or initiation interval > 255 does not fit ti_inst_rec"); return TI_ERR_INVALID_ARG; }
+  }
+  ti_ctx *c = new ti_ctx;
+  c->cfg = *cfg;
+  CK(cudaSetDevice(cfg->device));
+  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&c->ev0));
+  CK(cudaEventCreate(&c->ev1));
+  // one open-addressing table per architecture column
+  for (int col = 0; col < 5; ++col) {
+    std::vector<ti::IsaSlot> tab(ti::kIsaSlots);
+    memset(tab.data(), 0, tab.size() * sizeof(ti::IsaSlot));
+    for (const IsaRow &r : kIsaRows) {
+      if (!r.id[col]) continue;
+      uint64_t lo = 0;
+      uint32_t hi = 0;
+      const size_t n = strlen(r.name);
+      for (size_t i = 0; i < n; ++i) {
+        if (i < 8) lo |= (uint64_t)(uint8_t)r.name[i] << (8 * i);
+        else hi |= (uint32_t)(uint8_t)r.name[i] << (8 * (i - 8));
+      }
+      uint32_t h = ti::isa_hash(lo, hi);
+      while (tab[h].id) h = (h + 1) & (ti::kIsaSlots - 1);
+      tab[h].lo = lo; tab[h].hi = hi; tab[h].id = r.id[col]; tab[h].cat = r.cat[col];
+    }
+    CK(cudaMalloc((void **)&c->d_isa[col], tab.size() * sizeof(ti::IsaSlot)));
+    CK(cudaMemcpyAsync(c->d_isa[col], tab.data(), tab.size() * sizeof(ti::IsaSlot), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+  }
+  uint8_t spop[256];
+  memset(spop, 0, sizeof spop);
+  memcpy(spop, kSpopTable, sizeof kSpopTable < 256 ? sizeof kSpopTable : 256);
+  CK(cudaMalloc((void **)&c->d_spop, 256));
+  CK(cudaMemcpyAsync(c->d_spop, spop, 256, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  // persistent grid: every SM full of resident CTAs
+  CK(cudaFuncSetAttribute(ti::ti_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ti::kSmemBytes));
+  int sms = 0, per_sm = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->device));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ti::ti_decode_kernel, ti::kThreads, ti::kSmemBytes));
+  if (per_sm < 1) { ti::set_error("decode kernel does not fit on an SM"); return TI_ERR_CUDA; }
+  c->grid = sms * per_sm;
+  *out = c;
+  return TI_OK;
+}
+
+void ti_ctx_destroy(ti_ctx *c) {
+  if (!c) return;
+  for (auto &p : c->d_isa) if (p) cudaFree(p);
+  if (c->d_spop) cudaFree(c->d_spop);
+  if (c->ev0) cudaEventDestroy(c->ev0);
+  if (c->ev1) cudaEventDestroy(c->ev1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+static ti_status new_kernel(ti_ctx *ctx, const ti_kernel_hdr *hdr, ti_kernel **out) {
+  if (!ctx || !hdr || !out) return TI_ERR_INVALID_ARG;
+  const int col = arch_column(hdr->binary_version);
+  if (col < 0) {  // trace_driven.cc:113-118 prints this and exits
+    ti::set_error("unsupported binary version: %u", hdr->binary_version);
+    return TI_ERR_BINARY_VERSION;
+  }
+  ti_kernel *k = new ti_kernel;
+  k->ctx = ctx; k->hdr = *hdr; k->col = col;
+  memset(&k->counts, 0, sizeof k->counts);
+  memset(&k->host_counters, 0, sizeof k->host_counters);
+  *out = k;
+  return TI_OK;
+}
+
+ti_status ti_kernel_open_file(ti_ctx *ctx, const char *path, ti_kernel_hdr *hdr, ti_kernel **out) {
+  if (!ctx || !path || !out) return TI_ERR_INVALID_ARG;
+  FILE *f = fopen(path, "rb");
+  if (!f) { ti::set_error("Unable to open file: %s", path); return TI_ERR_IO; }  // trace_parser.cc:306-309
+  fseek(f, 0, SEEK_END);
+  const long n = ftell(f);
+  fseek(f, 0, SEEK_SET);
+  HostBuf img;
+  ti_status st = img.ensure((size_t)n + 16);
+  if (st != TI_OK) { fclose(f); return st; }
+  const size_t got = n ? fread(img.p, 1, (size_t)n, f) : 0;
+  fclose(f);
+  if (got != (size_t)n) { img.release(); ti::set_error("short read on %s", path); return TI_ERR_IO; }
+  ti_kernel_hdr h;
+  ti_parse_kernel_header((const char *)img.p, (size_t)n, &h);
+  if (hdr) *hdr = h;
+  st = new_kernel(ctx, &h, out);
+  if (st != TI_OK) { img.release(); return st; }
+  (*out)->h_file = img;
+  (*out)->h_body = (const char *)img.p + h.body_offset;
+  (*out)->body_len = (size_t)n - h.body_offset;
+  return TI_OK;
+}
+
+ti_status ti_kernel_open_buffer(ti_ctx *ctx, const char *body, size_t len, const ti_kernel_hdr *hdr, ti_kernel **out) {
+  if (!body && len) return TI_ERR_INVALID_ARG;
+  ti_status st = new_kernel(ctx, hdr, out);
+  if (st != TI_OK) return st;
+  (*out)->h_body = body;
+  (*out)->body_len = len;
+  return TI_OK;
+}
+
+ti_status ti_kernel_open_device(ti_ctx *ctx, const void *d_body, size_t len, const ti_kernel_hdr *hdr, ti_kernel **out) {
+  if ((!d_body && len) || ((uintptr_t)d_body & 15)) { ti::set_error("device body must be 16-byte aligned"); return TI_ERR_INVALID_ARG; }
+  ti_status st = new_kernel(ctx, hdr, out);
+  if (st != TI_OK) return st;
+  (*out)->d_borrowed = (const uint8_t *)d_body;
+  (*out)->body_len = len;
+  (*out)->sh_begin = 0; (*out)->sh_len = len; (*out)->uploaded = true;
+  return TI_OK;
+}
+
+void ti_kernel_close(ti_kernel *k) {
+  if (!k) return;
+  cudaStreamSynchronize(k->ctx->stream);
+  DevBuf *d[] = {&k->d_text, &k->inst, &k->rows, &k->txn_off, &k->txn, &k->tb, &k->warp, &k->state1, &k->state2, &k->globals, &k->counters};
+  for (DevBuf *b : d) b->release();
+  HostBuf *h[] = {&k->h_file, &k->h_inst, &k->h_rows, &k->h_txn_off, &k->h_txn, &k->h_tb, &k->h_warp, &k->h_small};
+  for (HostBuf *b : h) b->release();
+  delete k;
+}
+
+ti_status ti_kernel_upload(ti_kernel *k, size_t begin, size_t end) {
+  if (!k || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
+  if (end - begin > 0xfffffff0ull) { ti::set_error("shard of %zu bytes: cut it with ti_plan_shards", end - begin); return TI_ERR_TOO_LARGE; }
+  k->decoded = k->synced = k->retried = false;
+  if (k->d_borrowed) {
+    if (begin & 15) { ti::set_error("device-resident shards must start 16-byte aligned"); return TI_ERR_INVALID_ARG; }
+    k->sh_begin = begin; k->sh_len = end - begin; k->uploaded = true;
+    return TI_OK;
+  }
+  ti_status st = k->d_text.ensure(((end - begin + 15) & ~(size_t)15) + 16);
+  if (st != TI_OK) return st;
+  if (end > begin) CK(cudaMemcpyAsync(k->d_text.p, k->h_body + begin, end - begin, cudaMemcpyHostToDevice, k->ctx->stream));
+  k->sh_begin = begin; k->sh_len = end - begin; k->uploaded = true;
+  return TI_OK;
+}
+
+ti_status ti_kernel_decode(ti_kernel *k) {
+  if (!k) return TI_ERR_INVALID_ARG;
+  if (!k->uploaded) { ti::set_error("ti_kernel_decode before ti_kernel_upload"); return TI_ERR_STATE; }
+  const ti_config &cfg = k->ctx->cfg;
+  const double len = (double)k->sh_len;
+  // default capacities: the instruction bound is exact (no tracer line is shorter than 24
+  // bytes); the others are generous guesses, and a decode that overflows is re-run once
+  // with the exact counts the first pass measured (ti_kernel_sync).
+  if (!k->retried) {
+    k->cap_inst = (uint64_t)(len * (cfg.cap_inst_per_byte > 0 ? cfg.cap_inst_per_byte : 1.0 / 24)) + ti::kRecCap;
+    k->cap_mem = (uint64_t)(len * (cfg.cap_mem_per_byte > 0 ? cfg.cap_mem_per_byte : 1.0 / 32)) + ti::kRecCap;
+    k->cap_txn = (uint64_t)(len * (cfg.cap_txn_per_byte > 0 ? cfg.cap_txn_per_byte : 1.0 / 8)) + 4096;
+    k->cap_tb = (uint64_t)(len / 40) + 64;
+    k->cap_warp = (uint64_t)(len / 19) + 64;
+  }
+  return launch_decode(k);
+}
+
+ti_status ti_kernel_sync(ti_kernel *k, ti_counts *counts) {
+  if (!k) return TI_ERR_INVALID_ARG;
+  if (!k->decoded) { ti::set_error("ti_kernel_sync before ti_kernel_decode"); return TI_ERR_STATE; }
+  ti_ctx *c = k->ctx;
+  ti_status st = k->h_small.ensure(sizeof(ti::Globals) + sizeof(ti_counters));
+  if (st != TI_OK) return st;
+  ti::Globals *g = (ti::Globals *)k->h_small.p;
+  ti_counters *hc = (ti_counters *)((char *)k->h_small.p + sizeof(ti::Globals));
+  CK(cudaMemcpyAsync(g, k->globals.p, sizeof(ti::Globals), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(hc, k->counters.p, sizeof(ti_counters), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  CK(cudaGetLastError());
+  CK(cudaEventElapsedTime(&k->decode_ms, c->ev0, c->ev1));
+  if (g->overflow & 32) { ti::set_error("more than 2^32-2 records in one shard: cut it with ti_plan_shards"); return TI_ERR_TOO_LARGE; }
+  if (g->overflow) {
+    if (k->retried) { ti::set_error("output capacity exceeded twice (flags %u)", g->overflow); return TI_ERR_CAPACITY; }
+    // the first pass counted everything: size the arrays exactly and decode again
+    k->retried = true;
+    k->cap_inst = hc->n_inst + 1; k->cap_mem = hc->n_mem + 1; k->cap_txn = hc->n_txn + 1;
+    k->cap_tb = hc->n_tb + 1; k->cap_warp = hc->n_warp + 1;
+    st = launch_decode(k);
+    if (st != TI_OK) return st;
+    return ti_kernel_sync(k, counts);
+  }
+  k->host_counters = *hc;
+  memset(&k->counts, 0, sizeof k->counts);
+  k->counts.n_inst = hc->n_inst; k->counts.n_mem = hc->n_mem; k->counts.n_txn = hc->n_txn;
+  k->counts.n_tb = hc->n_tb; k->counts.n_warp = hc->n_warp; k->counts.text_bytes = k->sh_len;
+  uint32_t ef = g->error_flags;
+  if (hc->n_begin_tb != hc->n_end_tb || hc->n_begin_tb != hc->n_tb || hc->reserved[0] != hc->n_warp) ef |= TI_EF_BAD_STRUCTURE;
+  k->counts.error_flags = ef;
+  k->counts.first_error_line_off = g->first_error_off;
+  k->synced = true;
+  if (counts) *counts = k->counts;
+  if (ef) { ti::set_error("trace text outside the tracer grammar: flags 0x%x near shard offset %u", ef, g->first_error_off); return TI_ERR_PARSE; }
+  return TI_OK;
+}
+
+ti_status ti_kernel_fetch(ti_kernel *k, ti_view *v) {
+  if (!k || !v) return TI_ERR_INVALID_ARG;
+  if (!k->synced) { ti::set_error("ti_kernel_fetch before a successful ti_kernel_sync"); return TI_ERR_STATE; }
+  cudaStream_t s = k->ctx->stream;
+  const ti_counts &n = k->counts;
+  ti_status st;
+  if ((st = k->h_inst.ensure(n.n_inst * sizeof(ti_inst_rec))) != TI_OK) return st;
+  if ((st = k->h_rows.ensure(n.n_mem * 256)) != TI_OK) return st;
+  if ((st = k->h_txn_off.ensure((n.n_mem + 1) * 4)) != TI_OK) return st;
+  if ((st = k->h_txn.ensure(n.n_txn * sizeof(ti_txn_rec))) != TI_OK) return st;
+  if ((st = k->h_tb.ensure(n.n_tb * sizeof(ti_tb_rec))) != TI_OK) return st;
+  if ((st = k->h_warp.ensure(n.n_warp * sizeof(ti_warp_rec))) != TI_OK) return st;
+  if (n.n_inst) CK(cudaMemcpyAsync(k->h_inst.p, k->inst.p, n.n_inst * sizeof(ti_inst_rec), cudaMemcpyDeviceToHost, s));
+  if (n.n_mem) CK(cudaMemcpyAsync(k->h_rows.p, k->rows.p, n.n_mem * 256, cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(k->h_txn_off.p, k->txn_off.p, (n.n_mem + 1) * 4, cudaMemcpyDeviceToHost, s));
+  if (n.n_txn) CK(cudaMemcpyAsync(k->h_txn.p, k->txn.p, n.n_txn * sizeof(ti_txn_rec), cudaMemcpyDeviceToHost, s));
+  if (n.n_tb) CK(cudaMemcpyAsync(k->h_tb.p, k->tb.p, n.n_tb * sizeof(ti_tb_rec), cudaMemcpyDeviceToHost, s));
+  if (n.n_warp) CK(cudaMemcpyAsync(k->h_warp.p, k->warp.p, n.n_warp * sizeof(ti_warp_rec), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  v->text = k->h_body ? k->h_body + k->sh_begin : nullptr;
+  v->inst = (const ti_inst_rec *)k->h_inst.p;
+  v->addr_rows = (const uint64_t *)k->h_rows.p;
+  v->txn_off = (const uint32_t *)k->h_txn_off.p;
+  v->txn = (const ti_txn_rec *)k->h_txn.p;
+  v->tb = (const ti_tb_rec *)k->h_tb.p;
+  v->warp = (const ti_warp_rec *)k->h_warp.p;
+  v->counts = n;
+  return TI_OK;
+}
+
+ti_status ti_kernel_dev_view(ti_kernel *k, ti_dev_view *v) {
+  if (!k || !v) return TI_ERR_INVALID_ARG;
+  if (!k->synced) { ti::set_error("ti_kernel_dev_view before a successful ti_kernel_sync"); return TI_ERR_STATE; }
+  v->text = k->d_borrowed ? (const void *)(k->d_borrowed + k->sh_begin) : k->d_text.p;
+  v->inst = k->inst.p; v->addr_rows = k->rows.p; v->txn_off = k->txn_off.p; v->txn = k->txn.p;
+  v->tb = k->tb.p; v->warp = k->warp.p; v->counters = k->counters.p;
+  v->counts = k->counts;
+  return TI_OK;
+}
+
+ti_status ti_kernel_counters(ti_kernel *k, ti_counters *out) {
+  if (!k || !out) return TI_ERR_INVALID_ARG;
+  if (!k->synced) { ti::set_error("ti_kernel_counters before a successful ti_kernel_sync"); return TI_ERR_STATE; }
+  *out = k->host_counters;
+  return TI_OK;
+}
+
+ti_status ti_counters_finalize(const ti_ctx *ctx, const ti_counters *c, ti_power_counters *out) {
+  if (!ctx) return TI_ERR_INVALID_ARG;
+  return ti_counters_finalize_cfg(&ctx->cfg, c, out);
+}
+
+ti_status ti_kernel_timing(ti_kernel *k, float *decode_ms) {
+  if (!k || !decode_ms) return TI_ERR_INVALID_ARG;
+  if (!k->synced) return TI_ERR_STATE;
+  *decode_ms = k->decode_ms;
+  return TI_OK;
+}
+
+}  // extern "C"
+
+static ti_status launch_decode(ti_kernel *k) {
+  ti_ctx *c = k->ctx;
+  const ti_config &cfg = c->cfg;
+  cudaStream_t s = c->stream;
+  const uint32_t n_chunks = (uint32_t)((k->sh_len + ti::kChunk - 1) / ti::kChunk);
+  ti_status st;
+  if ((st = k->inst.ensure(k->cap_inst * sizeof(ti_inst_rec))) != TI_OK) return st;
+  if ((st = k->rows.ensure(k->cap_mem * 256)) != TI_OK) return st;
+  if ((st = k->txn_off.ensure((k->cap_mem + 1) * 4)) != TI_OK) return st;
+  if ((st = k->txn.ensure(k->cap_txn * sizeof(ti_txn_rec))) != TI_OK) return st;
+  if ((st = k->tb.ensure(k->cap_tb * sizeof(ti_tb_rec))) != TI_OK) return st;
+  if ((st = k->warp.ensure(k->cap_warp * sizeof(ti_warp_rec))) != TI_OK) return st;
+  if ((st = k->state1.ensure((size_t)(n_chunks + 1) * sizeof(ti::State1))) != TI_OK) return st;
+  if ((st = k->state2.ensure((size_t)(n_chunks + 1) * sizeof(ti::State2))) != TI_OK) return st;
+  if ((st = k->globals.ensure(sizeof(ti::Globals))) != TI_OK) return st;
+  if ((st = k->counters.ensure(sizeof(ti_counters))) != TI_OK) return st;
+
+  ti::DecodeParams P;
+  memset(&P, 0, sizeof P);
+  P.text = k->d_borrowed ? k->d_borrowed + k->sh_begin : (const uint8_t *)k->d_text.p;
+  P.len = k->sh_len;
+  P.n_chunks = n_chunks;
+  P.trace_version = k->hdr.trace_version;
+  P.shmem_base = k->hdr.shmem_base_addr; P.local_base = k->hdr.local_base_addr;
+  P.inst = (ti_inst_rec *)k->inst.p; P.cap_inst = k->cap_inst;
+  P.rows = (uint64_t *)k->rows.p; P.cap_mem = k->cap_mem;
+  P.txn_off = (uint32_t *)k->txn_off.p;
+  P.txn = (ti_txn_rec *)k->txn.p; P.cap_txn = k->cap_txn;
+  P.tb = (ti_tb_rec *)k->tb.p; P.cap_tb = k->cap_tb;
+  P.warp = (ti_warp_rec *)k->warp.p; P.cap_warp = k->cap_warp;
+  P.state1 = (ti::State1 *)k->state1.p; P.state2 = (ti::State2 *)k->state2.p;
+  P.g = (ti::Globals *)k->globals.p;
+  P.counters = (unsigned long long *)k->counters.p;
+  P.isa = c->d_isa[k->col]; P.spop = c->d_spop;
+  for (unsigned slot = 0; slot < 32; ++slot) {  // trace_driven.cc:441-480
+    const unsigned op = slot >= 18 ? 100 + (slot - 18) : slot;
+    const uint32_t *l = nullptr;
+    switch (op) {
+      case ti::OP_ALU: case ti::OP_INTP: case ti::OP_BRANCH: case ti::OP_CALL: case ti::OP_RET: l = cfg.lat_int; break;
+      case ti::OP_SP: l = cfg.lat_sp; break;
+      case ti::OP_DP: l = cfg.lat_dp; break;
+      case ti::OP_SFU: l = cfg.lat_sfu; break;
+      case ti::OP_TENSOR: l = cfg.lat_tensor; break;
+    }
+    if (op >= 100 && op < 108) l = cfg.lat_spec[op - 100];
+    P.lat[slot][0] = l ? (uint16_t)l[0] : 1; P.lat[slot][1] = l ? (uint16_t)l[1] : 1;
+  }
+  P.coalesce_arch = cfg.coalesce_arch; P.mem_warp_parts = cfg.mem_warp_parts; P.num_shmem_bank = cfg.num_shmem_bank;
+  P.shmem_limited_broadcast = cfg.shmem_limited_broadcast; P.gmem_skip_L1D = cfg.gmem_skip_L1D;
+
+  CK(cudaEventRecord(c->ev0, s));
+  CK(cudaMemsetAsync(k->state1.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s));
+  CK(cudaMemsetAsync(k->state2.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s));
+  CK(cudaMemsetAsync(k->globals.p, 0, sizeof(ti::Globals), s));
+  CK(cudaMemsetAsync(k->counters.p, 0, sizeof(ti_counters), s));
+  CK(cudaMemsetAsync(k->txn_off.p, 0, 4, s));
+  if (n_chunks) {
+    const int grid = (int)std::min<uint32_t>((uint32_t)c->grid, n_chunks);
+#ifdef TI_EMU
+    emu::launch(dim3(grid), dim3(ti::kThreads), ti::kSmemBytes, [=]() { ti::ti_decode_kernel(P); });
+    emu::launch(dim3(2), dim3(256), 0, [=]() { ti::ti_check_kernel((const ti_warp_rec *)k->warp.p, k->cap_warp, P.counters, P.g); });
+#else
+    ti::ti_decode_kernel<<<grid, ti::kThreads, ti::kSmemBytes, s>>>(P);
+    ti::ti_check_kernel<<<c->grid, 256, 0, s>>>((const ti_warp_rec *)k->warp.p, k->cap_warp, P.counters, P.g);
+#endif
+    CK(cudaGetLastError());
+  }
+  CK(cudaEventRecord(c->ev1, s));
+  k->decoded = true;
+  k->synced = false;
+  return TI_OK;
+}

@@ -1,0 +1,377 @@
+// Body of the fused kernel; included from ti_kernels.cuh.
+#ifndef TI_KERNEL_MAIN_CUH
+#define TI_KERNEL_MAIN_CUH
+
+namespace ti {
+
+TI_D void flush_counters(uint32_t *cnt, unsigned long long *g) {
+  for (int i = threadIdx.x; i < kSmCnt; i += kThreads) {
+    const uint32_t v = cnt[i];
+    if (v) {
+      // smem slots [0, kCntConst] mirror the same u64 words; then n_begin, n_end, smem_cycles and the
+      // number of "insts = n" lines (ti_counters.reserved[0], must equal the warp headers)
+      const int dst = i <= kCntConst ? i : (i == kCntConst + 1 ? kCntNInst + 5 : i == kCntConst + 2 ? kCntNInst + 6 : i == kCntConst + 3 ? kCntNInst + 8 : kCntNInst + 9);
+      atomicAdd(g + dst, (unsigned long long)v);
+      cnt[i] = 0;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams P) {
+  TI_DYN_SMEM(smem);
+  uint8_t *text = smem + oText;
+  uint4 *text_v = reinterpret_cast<uint4 *>(smem + oText);
+  ti_inst_rec *recs = reinterpret_cast<ti_inst_rec *>(smem + oRecs);
+  ti_txn_rec *stage = reinterpret_cast<ti_txn_rec *>(smem + oStage);
+  uint16_t *inst_off = reinterpret_cast<uint16_t *>(smem + oInstOff);
+  uint16_t *sl_off = reinterpret_cast<uint16_t *>(smem + oSlOff);
+  uint16_t *mem_list = reinterpret_cast<uint16_t *>(smem + oMemList);
+  uint16_t *txn_slot = reinterpret_cast<uint16_t *>(smem + oTxnSlot);
+  uint16_t *txn_loc = reinterpret_cast<uint16_t *>(smem + oTxnLoc);
+  uint8_t *txn_cnt = smem + oTxnCnt;
+  uint8_t *kind = smem + oKind;
+  uint32_t *cnt = reinterpret_cast<uint32_t *>(smem + oCnt);
+  uint16_t *nlmap = reinterpret_cast<uint16_t *>(smem + oNlMap);
+  const uint32_t *nlmap32 = reinterpret_cast<const uint32_t *>(smem + oNlMap);
+  uint16_t *tokpos = reinterpret_cast<uint16_t *>(smem + oTok) + (threadIdx.x >> 5) * 34;
+  Misc *ms = reinterpret_cast<Misc *>(smem + oMisc);
+
+  const unsigned tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int i = tid; i < kSmCnt; i += kThreads) cnt[i] = 0;
+  unsigned done_chunks = 0;
+
+  for (;;) {
+    __syncthreads();  // previous chunk fully drained (also orders the counter init)
+    if (tid == 0) {
+      ms->chunk = atomicAdd(&P.g->ticket, 1u);
+      ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0;
+    }
+    __syncthreads();
+    const uint32_t chunk = ms->chunk;
+    if (chunk >= P.n_chunks) break;
+    const uint64_t cb = (uint64_t)chunk * kChunk;            // text offset of the chunk
+    const uint32_t tbase = (uint32_t)(cb - 16);              // text offset = tbase + smem offset (mod 2^32)
+
+    // ---------------------------------------------------------------- P0 stage-in
+    for (int v = tid; v < kTextBytes / 16; v += kThreads) {
+      const int64_t pos = (int64_t)cb - 16 + (int64_t)v * 16;
+      uint4 x = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
+      if (v < (16 + kChunk + kSlack) / 16 && pos >= 0 && (uint64_t)pos < P.len) {
+        if ((uint64_t)pos + 16 <= P.len) x = __ldg(reinterpret_cast<const uint4 *>(P.text + pos));
+        else {
+          uint32_t w[4] = {0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au};
+          for (int b = 0; b < 16 && (uint64_t)pos + b < P.len; ++b)
+            w[b >> 2] = (w[b >> 2] & ~(0xffu << (8 * (b & 3)))) | (uint32_t)P.text[pos + b] << (8 * (b & 3));
+          x = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+      text_v[v] = x;
+    }
+    __syncthreads();
+
+    // ---------------------------------------------------------------- P1 line index
+    // A line start is a byte that follows '\n' and is not '\n' itself (blank lines
+    // never become lines, trace_parser.cc:408).  The newline bitmap of the whole
+    // staged region is kept (nlmap) so any thread can find the end of its line.
+    // Counts are packed 2 x 16 bit: instruction lines | structural lines.
+    const uint32_t lim = (uint32_t)(P.len - cb < (uint64_t)kChunk ? P.len - cb : (uint64_t)kChunk);
+    for (int v = tid; v < kTextBytes / 16; v += kThreads)
+      if (v == 0 || v > kChunk / 16) nlmap[v] = (uint16_t)nl_mask16(text_v[v]);
+    uint32_t starts[kVecIters];
+    uint32_t excl[kVecIters];
+    uint32_t run = 0;
+#pragma unroll
+    for (int it = 0; it < kVecIters; ++it) {
+      const uint32_t v = wid * (kVecIters * 32) + it * 32 + lane, s0 = v * 16;
+      const uint32_t m = nl_mask16(text_v[1 + v]);
+      nlmap[1 + v] = (uint16_t)m;
+      const uint32_t up = __shfl_up_sync(kFull, m, 1);
+      const uint32_t prev = lane ? (up >> 15) & 1 : (text[16 + s0 - 1] == '\n');
+      uint32_t st = ((m << 1) | prev) & ~m & 0xffffu;
+      if (s0 >= lim) st = 0;
+      else if (s0 + 16 > lim) st &= (1u << (lim - s0)) - 1;
+      uint32_t packed = 0;
+      for (uint32_t b = st; b; b &= b - 1) {
+        const unsigned c = text[16 + s0 + __ffs(b) - 1];
+        if (hexval(c) < 16) packed += 1u;
+        else {
+          packed += 1u << 16;
+          if (c == 't') atomicAdd(&ms->n_tb, 1u);
+          if (c == 'w') atomicAdd(&ms->n_warp, 1u);
+        }
+      }
+      uint32_t inc = packed;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { const uint32_t u = __shfl_up_sync(kFull, inc, d); if ((int)lane >= d) inc += u; }
+      starts[it] = st;
+      excl[it] = run + inc - packed;
+      run += __shfl_sync(kFull, inc, 31);
+    }
+    if (lane == 0) ms->warp_tot[wid] = run;
+    __syncthreads();
+    uint32_t pbase = 0, ptot = 0;
+    for (unsigned k = 0; k < (unsigned)kWarps; ++k) { const uint32_t t = (uint32_t)ms->warp_tot[k]; if (k < wid) pbase += t; ptot += t; }
+    uint32_t n_inst = ptot & 0xffff, n_sl = ptot >> 16, n_tb = ms->n_tb, n_warp = ms->n_warp;
+    const bool dense = n_inst > (uint32_t)kRecCap || n_sl > (uint32_t)kSlCap;
+    if (dense) {  // more lines than any tracer-written file can hold: flag, publish an empty chunk
+      if (tid == 0) note_error(ms, TI_EF_DENSE_CHUNK, (uint32_t)cb);
+      n_inst = n_sl = n_tb = n_warp = 0;
+    } else {
+#pragma unroll
+      for (int it = 0; it < kVecIters; ++it) {
+        const uint32_t s0 = (wid * (kVecIters * 32) + it * 32 + lane) * 16;
+        uint32_t at = pbase + excl[it];
+        for (uint32_t b = starts[it]; b; b &= b - 1) {
+          const uint32_t o = 16 + s0 + __ffs(b) - 1;
+          if (hexval(text[o]) < 16) { inst_off[at & 0xffff] = (uint16_t)o; at += 1; }
+          else { sl_off[at >> 16] = (uint16_t)o; at += 1u << 16; }
+        }
+      }
+    }
+    __syncthreads();
+
+    // ---------------------------------------------------------------- P2 tokenize
+    for (uint32_t io = tid; io < n_inst; io += kThreads) {
+      ti_inst_rec r;
+      unsigned kd;
+      const unsigned o = inst_off[io];
+      uint32_t fl = parse_inst_line(text, (int)o, P, tbase, r, kd);
+      if (line_end(nlmap32, o) - o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
+      if (fl) { note_error(ms, fl, tbase + o); kd = 0; r.mem_idx = 0xFFFFFFFFu; r.pack_c &= 0x7f; }
+      const uint4 *src = reinterpret_cast<const uint4 *>(&r);
+      uint4 *dst = reinterpret_cast<uint4 *>(recs + io);
+      dst[0] = src[0]; dst[1] = src[1];
+      kind[io] = (uint8_t)kd;
+    }
+    __syncthreads();
+
+    // ---------------------------------------------------------------- P3 memory-instruction ordinals
+    const uint32_t n_mem = block_scan(
+        n_inst, ms->warp_tot, [&](uint32_t i) { return (uint32_t)(kind[i] & 1); },
+        [&](uint32_t i, uint32_t ex, uint32_t v) { if (v) mem_list[ex] = (uint16_t)i; });
+
+    // ---------------------------------------------------------------- P4 look-back #1
+    if (wid == 0) {
+      const uint32_t agg[4] = {n_inst, n_mem, n_tb, n_warp};
+      uint64_t ex[4];
+      lookback<4>(P.state1, chunk, agg, ex);
+      if (lane == 0) { ms->base_inst = ex[0]; ms->base_mem = ex[1]; ms->base_tb = ex[2]; ms->base_warp = ex[3]; }
+    }
+    __syncthreads();
+    const uint64_t base_inst = ms->base_inst, base_mem = ms->base_mem, base_tb = ms->base_tb, base_warp = ms->base_warp;
+    if (tid == 0) {
+      uint32_t ov = 0;
+      if (base_inst + n_inst > P.cap_inst) ov |= 1;
+      if (base_mem + n_mem > P.cap_mem) ov |= 2;
+      if (base_tb + n_tb > P.cap_tb) ov |= 8;
+      if (base_warp + n_warp > P.cap_warp) ov |= 16;
+      if (base_inst + n_inst > 0xfffffffeull || base_mem + n_mem > 0xfffffffeull) ov |= 32;
+      if (ov) atomicOr(&P.g->overflow, ov);
+    }
+
+    // ---------------------------------------------------------------- P5 structural lines
+    // ordinals of "thread block" (low half) and "warp" (high half) lines among the structural lines
+    block_scan(
+        n_sl, ms->warp_tot,
+        [&](uint32_t i) { const unsigned c = text[sl_off[i]]; return (uint32_t)(c == 't' ? 1u : c == 'w' ? 0x10000u : 0u); },
+        [&](uint32_t i, uint32_t ex, uint32_t) {
+          const int o = sl_off[i];
+          int q = o;
+          const unsigned c = text[o];
+          uint32_t fl = 0;
+          // instruction lines before this one = its rank in the sorted inst_off list
+          uint32_t lo = 0, hi = n_inst;
+          while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (inst_off[mid] < o) lo = mid + 1; else hi = mid; }
+          const uint64_t first_inst = base_inst + lo;
+          if (c == '#') {
+            if (match_lit(text, q, "#BEGIN_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 1], 1u);
+            else { q = o; if (match_lit(text, q, "#END_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 2], 1u); else fl = TI_EF_BAD_STRUCTURE; }
+          } else if (c == 't') {                        // trace_parser.cc:423-427
+            ti_tb_rec r;
+            if (match_lit(text, q, "thread block = ") && parse_i32(text, q, r.x) && text[q++] == ',' &&
+                parse_i32(text, q, r.y) && text[q++] == ',' && parse_i32(text, q, r.z) && text[q] == '\n') {
+              r.text_off = cb - 16 + (uint64_t)o; r.line_len = (uint32_t)(q - o);
+              r.first_warp = (uint32_t)(base_warp + (ex >> 16)); r.first_inst = (uint32_t)first_inst;
+            } else { fl = TI_EF_BAD_STRUCTURE; r.text_off = cb - 16 + (uint64_t)o; r.x = r.y = r.z = 0; r.line_len = 0; r.first_warp = r.first_inst = 0; }
+            const uint64_t at = base_tb + (ex & 0xffff);
+            if (at < P.cap_tb) P.tb[at] = r;
+          } else if (c == 'w') {                        // trace_parser.cc:428-437
+            int32_t w = 0, n = 0;
+            bool ok = match_lit(text, q, "warp = ") && parse_i32(text, q, w) && text[q] == '\n' && w >= 0;
+            if (ok) {  // the next non-blank line must be "insts = n"
+              while (text[q] == '\n' && q < 16 + kChunk + kSlack) ++q;
+              ok = match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0;
+            }
+            if (!ok) { fl = TI_EF_BAD_STRUCTURE; w = n = 0; }
+            ti_warp_rec r;  // written even when malformed so the table never holds uninitialised rows
+            r.warp_id = (uint32_t)w; r.n_insts = (uint32_t)n; r.first_inst = (uint32_t)first_inst; r.reserved = 0;
+            const uint64_t at = base_warp + (ex >> 16);
+            if (at < P.cap_warp) P.warp[at] = r;
+          } else if (c == 'i') {
+            int32_t n = 0;
+            if (match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0) atomicAdd(&cnt[kCntConst + 4], 1u);
+            else fl = TI_EF_BAD_STRUCTURE;
+          } else fl = TI_EF_BAD_STRUCTURE;
+          if (line_end(nlmap32, (unsigned)o) - (unsigned)o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
+          note_error(ms, fl, tbase + (uint32_t)o);
+        });
+
+    // ---------------------------------------------------------------- P6 memory phase
+    for (;;) {
+      uint32_t mo = 0;
+      if (lane == 0) mo = atomicAdd(&ms->next_mem, 1u);
+      mo = __shfl_sync(kFull, mo, 0);
+      if (mo >= n_mem) break;
+      const uint32_t io = mem_list[mo];
+      ti_inst_rec *rp = recs + io;
+      const uint32_t mask = rp->mask, tmp = rp->mem_idx;
+      const unsigned mode = tmp >> 16 & 3, resolve = tmp >> 18 & 1;
+      unsigned op = rp->op, pack_c = rp->pack_c;
+      const unsigned ds = rp->data_size, pack_b = rp->pack_b;
+      __syncwarp();
+      uint32_t fl = 0;
+      const uint64_t addr = decode_addresses(text, tmp & 0xffff, mode, mask, tokpos, fl);
+      fl = __reduce_or_sync(kFull, fl);              // a bad token is seen by one lane only: make it warp-uniform
+      const uint64_t row = base_mem + mo;
+      if (row < P.cap_mem) P.rows[row * 32 + lane] = addr;
+      if (resolve) {                                 // trace_driven.cc:331-351
+        const uint64_t a0 = __shfl_sync(kFull, addr, __ffs(mask) - 1);
+        unsigned space = SPACE_GLOBAL, cache_op = CACHE_ALL;
+        if (a0 >= P.shmem_base && a0 < P.local_base) { space = SPACE_SHARED; cache_op = CACHE_UNDEF; }
+        else if (a0 >= P.local_base && a0 < P.local_base + (1u << 14)) space = SPACE_LOCAL;
+        pack_c = (pack_c & 0x80) | space | cache_op << 4;
+      }
+      const unsigned space = pack_c & 0xf, cache_op = pack_c >> 4 & 7;
+      unsigned n_txn = 0, cycles = 0;
+      Txn t2[2];
+      unsigned pos0 = lane, seg = 0;
+      const bool gated = (op == OP_LOAD || op == OP_STORE || op == OP_TLOAD || op == OP_TSTORE) && mask != 0;
+      const unsigned is_write = (op == OP_STORE || op == OP_TSTORE || (pack_b >> 4 & 3) == 2) ? 1u : 0u;
+      if (gated && !fl) {
+        if (space == SPACE_SHARED || space == SPACE_SSTARR) cycles = shared_cycles(P, mask, addr);
+        else if (space == SPACE_GLOBAL) {
+          seg = segment_size(P, ds, cache_op);
+          if (!seg) fl |= TI_EF_BAD_WIDTH;
+          else if (pack_b >> 6 & 1) n_txn = coalesce_atomic(P, mask, addr, ds, seg, t2[0], pos0, fl);
+          else n_txn = coalesce_global(P, mask, addr, ds, seg, t2);
+        } else if (space != SPACE_LOCAL) fl |= TI_EF_UNDEF_SPACE;
+      }
+      if (fl) n_txn = 0;                              // fl is warp-uniform here
+      uint32_t slot = 0;
+      if (lane == 0) {
+        note_error(ms, fl, rp->opc_off);
+        rp->mem_idx = (uint32_t)row; rp->pack_c = (uint8_t)pack_c; rp->cycles = (uint8_t)cycles;
+        slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
+        if (slot + n_txn > (uint32_t)kTxnStage) slot = 0xFFFFu;   // staging full: recomputed after look-back #2
+        txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
+      }
+      slot = __shfl_sync(kFull, slot, 0);
+      if (slot != 0xFFFFu) {
+        const unsigned type = is_write ? 4u : 0u;       // GLOBAL_ACC_W / GLOBAL_ACC_R
+        if (lane < n_txn) stage[slot + pos0] = reduce_and_send(t2[0], seg, type, is_write);
+        if (lane + 32 < n_txn) stage[slot + lane + 32] = reduce_and_send(t2[1], seg, type, is_write);
+      }
+    }
+    __syncthreads();
+
+    // ---------------------------------------------------------------- P7 look-back #2 + ordered copy-out
+    const uint32_t n_txn_chunk = block_scan(
+        n_mem, ms->warp_tot, [&](uint32_t i) { return (uint32_t)txn_cnt[i]; },
+        [&](uint32_t i, uint32_t ex, uint32_t) { txn_loc[i] = (uint16_t)ex; });
+    if (wid == 0) {
+      const uint32_t agg[1] = {n_txn_chunk};
+      uint64_t ex[1];
+      lookback<1>(P.state2, chunk, agg, ex);
+      if (lane == 0) ms->base_txn = ex[0];
+    }
+    __syncthreads();
+    const uint64_t base_txn = ms->base_txn;
+    if (tid == 0) {
+      uint32_t ov = 0;
+      if (base_txn + n_txn_chunk > P.cap_txn) ov |= 4;
+      if (base_txn + n_txn_chunk > 0xfffffffeull) ov |= 32;
+      if (ov) atomicOr(&P.g->overflow, ov);
+      if (chunk == P.n_chunks - 1) {                   // last chunk: CSR sentinel + totals
+        if (base_mem + n_mem <= P.cap_mem) P.txn_off[base_mem + n_mem] = (uint32_t)(base_txn + n_txn_chunk);
+        P.counters[kCntNInst + 0] = base_inst + n_inst; P.counters[kCntNInst + 1] = base_mem + n_mem;
+        P.counters[kCntNInst + 2] = base_txn + n_txn_chunk; P.counters[kCntNInst + 3] = base_tb + n_tb;
+        P.counters[kCntNInst + 4] = base_warp + n_warp; P.counters[kCntNInst + 7] = P.len;
+      }
+    }
+    for (uint32_t mo = tid; mo < n_mem; mo += kThreads)
+      if (base_mem + mo < P.cap_mem) P.txn_off[base_mem + mo] = (uint32_t)(base_txn + txn_loc[mo]);
+    // staged transactions: 16 B per thread, two threads per record
+    for (uint32_t mo = wid; mo < n_mem; mo += kWarps) {
+      const uint32_t n = txn_cnt[mo], slot = txn_slot[mo];
+      const uint64_t at = base_txn + txn_loc[mo];
+      if (!n) continue;
+      if (slot != 0xFFFFu) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(stage + slot);
+        uint4 *dst = reinterpret_cast<uint4 *>(P.txn + at);
+        for (uint32_t k = lane; k < 2 * n; k += 32)
+          if (at + (k >> 1) < P.cap_txn) dst[k] = src[k];
+      } else {
+        // overflowed the staging area: coalesce again from the row written in P6
+        const ti_inst_rec *rp = recs + mem_list[mo];
+        const uint64_t row = base_mem + mo;
+        const uint64_t addr = row < P.cap_mem ? __ldcg(P.rows + row * 32 + lane) : 0;
+        const unsigned ds = rp->data_size, pack_b = rp->pack_b, op = rp->op;
+        const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
+        const unsigned is_write = (op == OP_STORE || op == OP_TSTORE || (pack_b >> 4 & 3) == 2) ? 1u : 0u;
+        Txn t2[2];
+        unsigned pos0 = lane;
+        uint32_t fl = 0;
+        unsigned m;
+        if (pack_b >> 6 & 1) m = coalesce_atomic(P, rp->mask, addr, ds, seg, t2[0], pos0, fl);
+        else m = coalesce_global(P, rp->mask, addr, ds, seg, t2);
+        const unsigned type = is_write ? 4u : 0u;
+        if (lane < m && at + pos0 < P.cap_txn) P.txn[at + pos0] = reduce_and_send(t2[0], seg, type, is_write);
+        if (lane + 32 < m && at + lane + 32 < P.cap_txn) P.txn[at + lane + 32] = reduce_and_send(t2[1], seg, type, is_write);
+      }
+    }
+
+    // ---------------------------------------------------------------- P8 records out + counters
+    {
+      const uint4 *src = reinterpret_cast<const uint4 *>(recs);
+      uint4 *dst = reinterpret_cast<uint4 *>(P.inst + base_inst);
+      for (uint32_t k = tid; k < 2 * n_inst; k += kThreads)
+        if (base_inst + (k >> 1) < P.cap_inst) dst[k] = src[k];
+    }
+    for (uint32_t io = tid; io < n_inst; io += kThreads) {
+      const ti_inst_rec *rp = recs + io;
+      const unsigned op = rp->op, sp = rp->pack_a & 0x1f, act = __popc(rp->mask);
+      atomicAdd(&cnt[kCntHist + sp * 33 + act], 1u);
+      atomicAdd(&cnt[kCntOp + fold_op(op)], 1u);
+      if (op == OP_LOAD || op == OP_STORE || op == OP_MEMBAR || op == OP_TLOAD || op == OP_TSTORE) {
+        const unsigned st = (op == OP_STORE || op == OP_TSTORE || (rp->pack_b >> 4 & 3) == 2) ? 1u : 0u;
+        if (act) atomicAdd(&cnt[kCntSpace + (rp->pack_c & 0xf) * 2 + st], act);
+      }
+      if (rp->pack_b >> 7) atomicAdd(&cnt[kCntConst], 1u);
+      if (rp->cycles) atomicAdd(&cnt[kCntConst + 3], (uint32_t)rp->cycles);
+    }
+    if (tid == 0 && ms->err) {
+      atomicOr(&P.g->error_flags, ms->err);
+      atomicMin(&P.g->first_error_off, ms->first_err);
+    }
+    if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }
+  }
+  __syncthreads();
+  flush_counters(cnt, P.counters);
+}
+
+// Framing check over the finished warp-header table (the reference would trip an
+// assert or index past a vector, trace_parser.cc:435-443): every "insts = n" must be
+// followed by exactly n instruction lines.
+__global__ void ti_check_kernel(const ti_warp_rec *warp, uint64_t cap_warp, const unsigned long long *counters, Globals *g) {
+  const uint64_t n_warp = counters[kCntNInst + 4], n_inst = counters[kCntNInst + 0];
+  if (n_warp > cap_warp) return;  // the table overflowed: the host decodes again with exact capacities
+  const uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (uint64_t)gridDim.x * blockDim.x;
+  if (t0 == 0 && (n_warp ? warp[0].first_inst != 0 : n_inst != 0)) atomicOr(&g->error_flags, (uint32_t)TI_EF_FRAMING);
+  for (uint64_t k = t0; k < n_warp; k += stride) {
+    const uint64_t next = k + 1 < n_warp ? warp[k + 1].first_inst : n_inst;
+    if (next - warp[k].first_inst != warp[k].n_insts) atomicOr(&g->error_flags, (uint32_t)TI_EF_FRAMING);
+  }
+}
+
+}  // namespace ti
+#endif

@@ -1,0 +1,196 @@
+// The fused trace-ingest kernel (see ti_device.cuh for the data layout and the plan).
+//
+// Per chunk, one CTA runs these phases entirely out of shared memory:
+//   P0 stage-in   16 B vector loads of [chunk-16, chunk+CHUNK+slack) -> smem
+//   P1 line index newline bitmap (SIMD byte compare) -> line-start lists, by class
+//   P2 tokenize   thread-per-line decode of instruction lines -> 32 B records (smem)
+//   P3 compact    ordinal of every memory instruction (ballot scans)
+//   P4 look-back  chained scan #1 -> global offsets for inst / mem / tb / warp
+//   P5 structure  "thread block" / "warp"+"insts" / "#BEGIN_TB" / "#END_TB" lines
+//   P6 memory     warp-per-instruction: addresses -> 256 B row, coalescer -> smem
+//   P7 look-back  chained scan #2 over transaction counts, ordered copy-out
+//   P8 stage-out  records smem -> HBM with 16 B coalesced stores, counters
+#ifndef TI_KERNELS_CUH
+#define TI_KERNELS_CUH
+
+#include "ti_device.cuh"
+#include "ti_mem.cuh"
+#include "ti_parse.cuh"
+
+#ifdef TI_EMU
+#define TI_DYN_SMEM(p) unsigned char *p = emu::cur_smem()
+static inline unsigned __vcmpeq4(unsigned a, unsigned b) {
+  unsigned r = 0;
+  for (int i = 0; i < 4; ++i)
+    if (((a >> (8 * i)) & 0xff) == ((b >> (8 * i)) & 0xff)) r |= 0xffu << (8 * i);
+  return r;
+}
+#else
+#define TI_DYN_SMEM(p) extern __shared__ __align__(16) unsigned char ti_smem_raw_[]; unsigned char *p = ti_smem_raw_
+#endif
+
+namespace ti {
+
+// ------------------------------------------------------------ shared-memory plan
+struct Misc {
+  uint64_t base_inst, base_mem, base_tb, base_warp, base_txn;
+  uint64_t warp_tot[kWarps];
+  uint32_t chunk, n_inst, n_sl, n_mem, n_tb, n_warp, n_txn;
+  uint32_t next_mem, stage_used, err, first_err;
+};
+constexpr int align16(int x) { return (x + 15) & ~15; }
+constexpr int oText = 0;
+constexpr int oRecs = oText + kTextBytes;
+constexpr int oStage = oRecs + kRecCap * 32;
+constexpr int oInstOff = oStage + kTxnStage * 32;            // u16[kRecCap]  smem offset of each instruction line
+constexpr int oSlOff = oInstOff + align16(kRecCap * 2);      // u16[kSlCap]   smem offset of each structural line
+constexpr int oMemList = oSlOff + align16(kSlCap * 2);       // u16[kRecCap]  record index of each memory instruction
+constexpr int oTxnSlot = oMemList + align16(kRecCap * 2);    // u16[kRecCap]  staging slot (0xFFFF = recompute later)
+constexpr int oTxnLoc = oTxnSlot + align16(kRecCap * 2);     // u16[kRecCap]  exclusive txn offset inside the chunk
+constexpr int oTxnCnt = oTxnLoc + align16(kRecCap * 2);      // u8 [kRecCap]
+constexpr int oKind = oTxnCnt + align16(kRecCap);            // u8 [kRecCap]  bit0 = has addresses
+constexpr int oCnt = oKind + align16(kRecCap);               // u32[kSmCnt]   counter mirror
+constexpr int oTok = oCnt + align16(kSmCnt * 4);             // u16[kWarps][34]
+constexpr int oNlMap = oTok + align16(kWarps * 34 * 2);      // u16[kTextBytes/16] newline bitmap of the staged text
+constexpr int oMisc = oNlMap + align16(kTextBytes / 16 * 2 + 4);
+constexpr int kSmemBytes = oMisc + align16((int)sizeof(Misc));
+static_assert(kTextBytes % 16 == 0 && (kChunk / 16) % kThreads == 0, "chunk geometry");
+static_assert(kTextBytes < 65536, "smem offsets are 16 bit");
+constexpr int kVecIters = kChunk / 16 / kThreads;
+
+TI_D uint32_t ld_flag(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
+TI_D uint32_t ld_vol(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
+TI_D uint64_t ld_vol(const uint64_t *p) { return *reinterpret_cast<const volatile uint64_t *>(p); }
+
+TI_D uint64_t warp_sum_u64(uint64_t v) {
+#pragma unroll
+  for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(kFull, v, d);
+  return v;
+}
+
+// Chained scan with decoupled look-back (single pass): publishes this chunk's
+// aggregate, sums the aggregates of the predecessors that have not finished yet
+// plus the nearest published inclusive prefix, then publishes its own inclusive
+// prefix.  Chunks are handed out in order by the ticket, so every predecessor is
+// already running.  Executed by one full warp.
+template <int NV>
+TI_D void lookback(LookBack<NV> *st, uint32_t c, const uint32_t (&agg)[NV], uint64_t (&excl)[NV]) {
+  const unsigned lane = lane_id();
+#pragma unroll
+  for (int k = 0; k < NV; ++k) excl[k] = 0;
+  if (c == 0) {
+    if (lane == 0) {
+      for (int k = 0; k < NV; ++k) { st[0].agg[k] = agg[k]; st[0].incl[k] = agg[k]; }
+      __threadfence();
+      atomicExch(&st[0].flag, 2u);
+    }
+    __syncwarp();
+    return;
+  }
+  if (lane == 0) {
+    for (int k = 0; k < NV; ++k) st[c].agg[k] = agg[k];
+    __threadfence();
+    atomicExch(&st[c].flag, 1u);
+  }
+  for (int64_t idx = (int64_t)c - 1;; idx -= 32) {
+    const int64_t j = idx - lane;
+    uint32_t f;
+    for (;;) {
+      f = j >= 0 ? ld_flag(&st[j].flag) : 2u;
+      if (!__any_sync(kFull, f == 0)) break;
+      __nanosleep(40);
+    }
+    __threadfence();
+    const uint32_t have = __ballot_sync(kFull, f == 2);
+    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      uint64_t v = 0;
+      if (j >= 0 && lane < L) v = ld_vol(&st[j].agg[k]);
+      else if (j >= 0 && lane == L) v = ld_vol(&st[j].incl[k]);
+      excl[k] += warp_sum_u64(v);
+    }
+    if (L < 32) break;
+  }
+  if (lane == 0) {
+    for (int k = 0; k < NV; ++k) st[c].incl[k] = excl[k] + agg[k];
+    __threadfence();
+    atomicExch(&st[c].flag, 2u);
+  }
+  __syncwarp();
+}
+
+TI_D void note_error(Misc *ms, uint32_t flags, uint32_t off) {
+  if (!flags) return;
+  atomicOr(&ms->err, flags);
+  atomicMin(&ms->first_err, off);
+}
+
+// newline bitmap of 16 bytes
+TI_D uint32_t nl_mask16(const uint4 x) {
+  const uint32_t a = __vcmpeq4(x.x, 0x0a0a0a0au) & 0x01010101u, b = __vcmpeq4(x.y, 0x0a0a0a0au) & 0x01010101u;
+  const uint32_t c = __vcmpeq4(x.z, 0x0a0a0a0au) & 0x01010101u, d = __vcmpeq4(x.w, 0x0a0a0a0au) & 0x01010101u;
+  return ((a * 0x00204081u >> 21) & 0xf) | ((b * 0x00204081u >> 21) & 0xf) << 4 |
+         ((c * 0x00204081u >> 21) & 0xf) << 8 | ((d * 0x00204081u >> 21) & 0xf) << 12;
+}
+
+// Exclusive scan of small per-item values over items [0, n), in item order, by the
+// whole CTA (two ballot-free passes, one barrier).  val(i) is evaluated twice.
+template <class V, class E>
+TI_D uint32_t block_scan(uint32_t n, uint64_t *warp_tot, V val, E emit) {
+  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
+  const uint32_t seg = ((n + kWarps - 1) / kWarps + 31) & ~31u;
+  const uint32_t lo = w * seg, hi = lo + seg < n ? lo + seg : n;
+  uint32_t tot = 0;
+  for (uint32_t i = lo + lane; i < lo + seg && lo < n; i += 32) {
+    uint32_t v = i < hi ? val(i) : 0;
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(kFull, v, d);
+    tot += v;
+  }
+  if (lane == 0) warp_tot[w] = tot;
+  __syncthreads();
+  uint32_t base = 0, total = 0;
+  for (unsigned k = 0; k < (unsigned)kWarps; ++k) { const uint32_t t = (uint32_t)warp_tot[k]; if (k < w) base += t; total += t; }
+  for (uint32_t i = lo + lane; i < lo + seg && lo < n; i += 32) {
+    const uint32_t v = i < hi ? val(i) : 0;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t up = __shfl_up_sync(kFull, inc, d); if ((int)lane >= d) inc += up; }
+    if (i < hi) emit(i, base + inc - v, v);
+    base += __shfl_sync(kFull, inc, 31);
+  }
+  __syncthreads();
+  return total;
+}
+
+// smem offset of the first '\n' at or after offset o (the sentinel guarantees one)
+TI_D unsigned line_end(const uint32_t *nlmap32, unsigned o) {
+  unsigned w = o >> 5;
+  uint32_t bits = nlmap32[w] >> (o & 31);
+  if (bits) return o + __ffs(bits) - 1;
+  do bits = nlmap32[++w]; while (!bits);
+  return (w << 5) + __ffs(bits) - 1;
+}
+
+TI_D bool match_lit(const uint8_t *t, int &q, const char *s) {
+  for (; *s; ++s, ++q) if (t[q] != (uint8_t)*s) return false;
+  return true;
+}
+TI_D bool parse_i32(const uint8_t *t, int &q, int32_t &v) {  // optional '-', <= 10 digits, fits int32
+  const bool neg = t[q] == '-';
+  if (neg) ++q;
+  int64_t m = 0;
+  int nd = 0;
+  unsigned d;
+  while ((d = t[q] - '0') <= 9) { m = m * 10 + d; ++q; if (++nd > 10) return false; }
+  if (!nd || m > 0x7fffffffLL + (neg ? 1 : 0)) return false;
+  v = (int32_t)(neg ? -m : m);
+  return true;
+}
+
+}  // namespace ti
+
+#include "ti_kernel_main.cuh"
+
+#endif

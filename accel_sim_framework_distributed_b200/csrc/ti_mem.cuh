@@ -1,0 +1,269 @@
+// Warp-per-instruction memory phase of the fused trace-ingest kernel: lane i owns
+// trace lane i of one memory instruction.
+//   * address decompression (trace_parser.cc:86-125,181-209): list / base+stride /
+//     base+delta, tokens located with ballots over the address text in smem
+//   * shared-memory bank conflicts (abstract_hardware_model.cc:329-420)
+//   * global coalescing into 32 B sectors / 64 B / 128 B segments incl. the
+//     straddle rule and the ascending emit order (:475-586), atomics (:588-692) and
+//     the size reduction (:694-748)
+#ifndef TI_MEM_CUH
+#define TI_MEM_CUH
+
+#include "ti_device.cuh"
+#include "ti_parse.cuh"
+
+namespace ti {
+
+constexpr unsigned kFull = 0xffffffffu;
+
+struct Txn {  // a transaction_info (abstract_hardware_model.h:1131-1141) in registers
+  uint64_t block;
+  uint32_t lanes, bytes[4], chunks;
+};
+
+TI_D unsigned lane_id() { return threadIdx.x & 31; }
+TI_D unsigned lanemask_lt() { return (1u << lane_id()) - 1; }
+
+// 64-bit warp minimum from two 32-bit redux steps
+TI_D uint64_t warp_min_u64(uint64_t v) {
+  const uint32_t hi = __reduce_min_sync(kFull, (uint32_t)(v >> 32));
+  const uint32_t lo = __reduce_min_sync(kFull, (uint32_t)(v >> 32) == hi ? (uint32_t)v : 0xffffffffu);
+  return (uint64_t)hi << 32 | lo;
+}
+
+// bits [idx, idx+n) of a 128-bit mask, clipped at 128, as four words
+TI_D void byte_words(unsigned idx, unsigned n, uint32_t w[4]) {
+  w[0] = w[1] = w[2] = w[3] = 0;
+  const uint64_t v = (uint64_t)((1u << n) - 1) << (idx & 31);
+  const unsigned k = idx >> 5;
+  w[k] = (uint32_t)v;
+  if (k < 3) w[k + 1] = (uint32_t)(v >> 32);
+}
+
+// abstract_hardware_model.cc:482-507
+TI_D unsigned segment_size(const DecodeParams &P, unsigned data_size, unsigned cache_op) {
+  bool sector = false;
+  if (P.coalesce_arch >= 20 && P.coalesce_arch < 39) sector = P.gmem_skip_L1D || cache_op == CACHE_GLOBAL;
+  else if (P.coalesce_arch >= 40) sector = true;
+  switch (data_size) {
+    case 1: return 32;
+    case 2: return sector ? 32 : 64;
+    case 4: case 8: case 16: return sector ? 32 : 128;
+  }
+  return 0;
+}
+
+// abstract_hardware_model.cc:694-748
+TI_D ti_txn_rec reduce_and_send(const Txn &t, unsigned seg, unsigned type, unsigned is_write) {
+  uint64_t addr = t.block;
+  unsigned size = seg, q = t.chunks, h = 0;
+  if (seg == 128) {
+    const bool lo = q & 3, hi = q & 12;
+    if (lo && !hi) { size = 64; h = q & 3; }
+    else if (!lo && hi) { addr += 64; size = 64; h = (q >> 2) & 3; }
+  } else if (seg == 64) {
+    h = (addr % 128 == 0) ? (q & 3) : ((q >> 2) & 3);
+  }
+  if (size == 64) {
+    const bool lo = h & 1, hi = h & 2;
+    if (lo && !hi) size = 32;
+    else if (!lo && hi) { addr += 32; size = 32; }
+  }
+  ti_txn_rec r;
+  r.addr = addr; r.lane_mask = t.lanes;
+  r.byte_mask[0] = t.bytes[0]; r.byte_mask[1] = t.bytes[1]; r.byte_mask[2] = t.bytes[2]; r.byte_mask[3] = t.bytes[3];
+  r.size = (uint8_t)size; r.sector_mask = (uint8_t)t.chunks; r.type = (uint8_t)type; r.is_write = (uint8_t)is_write;
+  return r;
+}
+
+// ---- address decompression.  `q` = smem offset of the first token after the mode
+// field; tokpos = 33 u16 of per-warp scratch.  Returns this lane's address.
+TI_D uint64_t decode_addresses(const uint8_t *text, unsigned q, unsigned mode, uint32_t mask, uint16_t *tokpos,
+                               uint32_t &flags) {
+  const unsigned lane = lane_id();
+  const bool active = mask >> lane & 1;
+  if (mode == 1) {  // every lane reads the same two tokens (smem broadcast)
+    Reader rd = {text, (int)q};
+    uint64_t base = 0;
+    int64_t stride = 0;
+    rd.skip_ws();
+    if (rd.peek() != '\n') {
+      if (!rd.hex(16, base)) { flags |= TI_EF_BAD_NUMBER; return 0; }
+      rd.skip_ws();
+      if (rd.peek() != '\n' && !rd.sdec(0x7fffffffull, stride)) { flags |= TI_EF_BAD_NUMBER; return 0; }
+    }
+    if (!mask) return 0;
+    const unsigned first = __ffs(mask) - 1;
+    const uint32_t inv = ~(mask >> first);          // zero bit = still inside the first run
+    const unsigned run = inv ? __ffs(inv) - 1 : 32; // length of the first contiguous run
+    if (lane < first || lane >= first + run) return 0;  // incl. active lanes after the gap
+    return base + (uint64_t)stride * (uint64_t)(lane - first);
+  }
+  if (mode != 0 && mode != 2) return 0;             // value-initialised addresses stay 0
+  // ---- list / delta: token k belongs to the k-th active lane
+  const unsigned nact = __popc(mask);
+  const unsigned rank = __popc(mask & lanemask_lt());
+  unsigned ntok = 0;
+  unsigned prev_ws = 1;                              // q follows a delimiter
+  for (unsigned base = q;; base += 32) {
+    const unsigned c = text[base + lane];
+    const unsigned nlb = __ballot_sync(kFull, c == '\n');
+    unsigned wsb = __ballot_sync(kFull, is_end(c));
+    const unsigned valid = nlb ? ((1u << (__ffs(nlb) - 1)) - 1) : kFull;  // bytes before the newline
+    const unsigned start = ~wsb & (wsb << 1 | prev_ws) & valid;
+    if (start >> lane & 1) {
+      const unsigned k = ntok + __popc(start & lanemask_lt());
+      if (k < 33) tokpos[k] = (uint16_t)(base + lane);
+    }
+    ntok += __popc(start);
+    prev_ws = wsb >> 31;
+    if (nlb || ntok >= nact) break;
+  }
+  __syncwarp();
+  uint64_t val = 0;
+  if (active && rank < ntok) {
+    Reader rd = {text, (int)tokpos[rank]};
+    bool ok;
+    if (mode == 0 || rank == 0) ok = rd.hex(16, val);
+    else { int64_t d; ok = rd.sdec(0x7fffffffffffffffull, d); val = (uint64_t)d; }
+    if (!ok) flags |= TI_EF_BAD_NUMBER;
+  }
+  __syncwarp();
+  if (mode == 0) return active ? val : 0;
+  // base + running sum of deltas over the active lanes (wraps mod 2^64)
+  uint64_t sum = active ? val : 0;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint64_t up = __shfl_up_sync(kFull, sum, d);
+    if ((int)lane >= d) sum += up;
+  }
+  return active ? sum : 0;
+}
+
+// ---- shared-memory bank conflicts: returns `cycles` (warp-uniform)
+TI_D unsigned shared_cycles(const DecodeParams &P, uint32_t mask, uint64_t addr) {
+  const unsigned lane = lane_id();
+  const unsigned parts = (unsigned)P.mem_warp_parts, sub = 32 / parts;
+  const uint64_t word = addr & ~3ull;
+  const unsigned bank = (unsigned)((addr / 4) % (unsigned)P.num_shmem_bank);
+  unsigned total = 0;
+  for (unsigned p = 0; p < parts; ++p) {
+    const uint32_t pm = (sub == 32 ? kFull : ((1u << sub) - 1) << (p * sub)) & mask;
+    if (!pm) continue;                                   // warp-uniform
+    const bool in = pm >> lane & 1;
+    unsigned grp = 0, nword = 0;
+    bool leader = false;
+    if (in) {
+      grp = __match_any_sync(pm, word);                  // lanes touching the same word
+      leader = (unsigned)(__ffs(grp) - 1) == lane;
+      nword = __popc(grp);
+    }
+    unsigned acc = 0;
+    if (!P.shmem_limited_broadcast) {
+      const uint32_t lm = __ballot_sync(kFull, leader);
+      if (leader) acc = __popc(__match_any_sync(lm, bank));  // distinct words per bank
+    } else {
+      // first (bank, word) in ascending order that more than one lane reads
+      const bool multi = leader && nword > 1;
+      const unsigned bbank = __reduce_min_sync(kFull, multi ? bank : 0xffffffffu);
+      uint64_t bword = 0;
+      unsigned bn = 0;
+      if (bbank != 0xffffffffu) {
+        bword = warp_min_u64(multi && bank == bbank ? word : ~0ull);
+        const uint32_t who = __ballot_sync(kFull, multi && bank == bbank && word == bword);
+        bn = __shfl_sync(kFull, nword, __ffs(who) - 1);
+      }
+      if (in) {
+        acc = __popc(__match_any_sync(pm, bank));        // lanes per bank
+        if (bbank != 0xffffffffu && bank == bbank) acc -= bn - 1;
+      }
+    }
+    total += __reduce_max_sync(kFull, acc);
+  }
+  return total;
+}
+
+// ---- global coalescing.  Each lane may end up holding up to two finished
+// transactions (index n lives in lane n % 32, slot n / 32).  Returns the count.
+TI_D unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_t addr, unsigned ds, unsigned seg,
+                              Txn out[2]) {
+  const unsigned lane = lane_id();
+  const unsigned parts = (unsigned)P.mem_warp_parts, sub = 32 / parts;
+  const uint64_t segmask = ~(uint64_t)(seg - 1);
+  const uint64_t last = addr + ds - 1;
+  const uint64_t keyA = addr & segmask, keyB = last & segmask;
+  const bool act = (mask >> lane & 1) && addr != 0;      // abstract_hardware_model.cc:534-537
+  uint32_t wa[4], wb[4];
+  byte_words((unsigned)(addr & 127), ds, wa);
+  byte_words((unsigned)(last & 127), ds, wb);            // the straddle rule, :559-571
+  const unsigned ca = 1u << ((addr & 127) / 32), cb = 1u << ((last & 127) / 32);
+  unsigned n = 0;
+  for (unsigned p = 0; p < parts; ++p) {
+    const bool in = sub == 32 || (lane / sub) == p;
+    bool pendA = act && in, pendB = pendA && keyA != keyB;
+    while (__ballot_sync(kFull, pendA || pendB)) {
+      uint64_t km = ~0ull;
+      if (pendA) km = keyA;
+      if (pendB && keyB < km) km = keyB;
+      const uint64_t cur = warp_min_u64(km);             // std::map order: ascending block address
+      const bool hitA = pendA && keyA == cur, hitB = pendB && keyB == cur;
+      Txn t;
+      t.block = cur;
+      t.lanes = __ballot_sync(kFull, hitA || hitB);
+#pragma unroll
+      for (int w = 0; w < 4; ++w) t.bytes[w] = __reduce_or_sync(kFull, (hitA ? wa[w] : 0u) | (hitB ? wb[w] : 0u));
+      t.chunks = __reduce_or_sync(kFull, (hitA ? ca : 0u) | (hitB ? cb : 0u));
+      if (lane == (n & 31)) out[n >> 5] = t;
+      ++n;
+      pendA = pendA && !hitA;
+      pendB = pendB && !hitB;
+    }
+  }
+  return n;
+}
+
+// ---- atomics: order-dependent first fit per block (abstract_hardware_model.cc:626-673).
+// Transaction k lives in lane k; `pos` receives its emit position.  Returns the count,
+// or sets TI_EF_ATOMIC_STRADDLE.
+TI_D unsigned coalesce_atomic(const DecodeParams &P, uint32_t mask, uint64_t addr, unsigned ds, unsigned seg, Txn &mine,
+                              unsigned &pos, uint32_t &flags) {
+  const unsigned lane = lane_id();
+  const unsigned parts = (unsigned)P.mem_warp_parts, sub = 32 / parts;
+  const uint64_t segmask = ~(uint64_t)(seg - 1);
+  unsigned n = 0;
+  mine.block = 0; mine.lanes = 0; mine.chunks = 0; mine.bytes[0] = mine.bytes[1] = mine.bytes[2] = mine.bytes[3] = 0;
+  pos = 0;
+  for (unsigned p = 0; p < parts; ++p) {
+    const unsigned first_of_part = n;
+    for (unsigned t = p * sub; t < (p + 1) * sub; ++t) {
+      if (!(mask >> t & 1)) continue;                    // warp-uniform
+      const uint64_t a = __shfl_sync(kFull, addr, t);
+      const uint64_t blk = a & segmask;
+      if (blk != ((a + ds - 1) & segmask)) { flags |= TI_EF_ATOMIC_STRADDLE; return 0; }
+      uint32_t tw[4];
+      byte_words((unsigned)(a & 127), ds, tw);
+      const bool cand = lane >= first_of_part && lane < n && mine.block == blk &&
+                        !((mine.bytes[0] & tw[0]) | (mine.bytes[1] & tw[1]) | (mine.bytes[2] & tw[2]) | (mine.bytes[3] & tw[3]));
+      const uint32_t cbm = __ballot_sync(kFull, cand);
+      const unsigned k = cbm ? (unsigned)(__ffs(cbm) - 1) : n;
+      if (lane == k) {
+        if (!cbm) mine.block = blk;
+        mine.bytes[0] |= tw[0]; mine.bytes[1] |= tw[1]; mine.bytes[2] |= tw[2]; mine.bytes[3] |= tw[3];
+        mine.lanes |= 1u << t;
+        mine.chunks |= 1u << ((a & 127) / 32);
+      }
+      if (!cbm) ++n;
+    }
+    // emit order inside the part: ascending block, then creation order
+    unsigned rank = 0;
+    for (unsigned j = first_of_part; j < n; ++j) {
+      const uint64_t bj = __shfl_sync(kFull, mine.block, j);
+      rank += (bj < mine.block) || (bj == mine.block && j < lane);
+    }
+    if (lane >= first_of_part && lane < n) pos = first_of_part + rank;
+  }
+  return n;
+}
+
+}  // namespace ti
+#endif

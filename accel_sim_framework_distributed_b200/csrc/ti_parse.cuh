@@ -1,0 +1,271 @@
+// Thread-per-line tokenizer + instruction decode of the fused trace-ingest kernel.
+//
+// One thread walks one instruction line held in shared memory and produces the
+// 32-byte ti_inst_rec: every field of inst_trace_t::parse_from_string
+// (trace_parser.cc:127-214) and of trace_warp_inst_t::parse_from_trace_struct
+// (trace_driven.cc:151-381) that does not need the decompressed addresses.  Address
+// lists are left for the warp-per-instruction memory phase (ti_mem.cuh): only the
+// offset of the first address token and the compression mode are recorded.
+//
+// Thread-per-line (not warp-per-line) because a ~50-byte line is ~450 scalar
+// instructions of inherently sequential work: 32 lines per warp keep all lanes busy,
+// a warp per line would idle most of them.
+#ifndef TI_PARSE_CUH
+#define TI_PARSE_CUH
+
+#include "ti_device.cuh"
+
+#define TI_OPCODE_IDS_ONLY
+#define TI_ISA_BEGIN
+#define TI_ISA_ROW(...)
+#define TI_ISA_END
+#define TI_SPOP_BEGIN
+#define TI_SPOP(...)
+#define TI_SPOP_END
+#include "isa_tables.inc"
+#undef TI_ISA_BEGIN
+#undef TI_ISA_ROW
+#undef TI_ISA_END
+#undef TI_SPOP_BEGIN
+#undef TI_SPOP
+#undef TI_SPOP_END
+
+namespace ti {
+
+TI_HD bool is_ws(unsigned c) { return c == ' ' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
+TI_HD bool is_end(unsigned c) { return c == '\n' || is_ws(c); }
+TI_HD unsigned hexval(unsigned c) {  // 0..15, or >= 16 when not a hex digit
+  unsigned d = c - '0';
+  if (d <= 9) return d;
+  d = (c | 0x20) - 'a';
+  return d <= 5 ? d + 10 : 255u;
+}
+
+constexpr uint64_t pack8(const char *s) {
+  uint64_t v = 0;
+  for (int i = 0; i < 8 && s[i]; ++i) v |= (uint64_t)(unsigned char)s[i] << (8 * i);
+  return v;
+}
+
+// Per-instruction scratch handed to the memory phase through the record's mem_idx
+// field (overwritten with the real row index before the record leaves smem).
+//   [15:0] smem offset of the first token after the address-mode field
+//   [17:16] address mode (0 list, 1 base+stride, 2 base+delta, 3 other)
+//   [18] generic LD/ST whose space depends on the first active address
+TI_HD uint32_t memtmp_make(unsigned q, unsigned mode, bool resolve) {
+  return q | (mode > 3 ? 3u : mode) << 16 | (resolve ? 1u : 0u) << 18;
+}
+
+struct Reader {
+  const uint8_t *t;
+  int q;
+  TI_D unsigned peek() const { return t[q]; }
+  TI_D void skip_ws() { while (is_ws(t[q])) ++q; }
+  TI_D void skip_token() { while (!is_end(t[q])) ++q; }
+  // unsigned decimal, <= 19 digits, value <= max; the token must end right after
+  TI_D bool dec(uint64_t max, uint64_t &v) {
+    int nd = 0;
+    uint64_t m = 0;
+    unsigned d;
+    while ((d = t[q] - '0') <= 9) { m = m * 10 + d; ++q; if (++nd > 19) return false; }
+    v = m;
+    return nd > 0 && is_end(t[q]) && m <= max;
+  }
+  TI_D bool sdec(uint64_t max_pos, int64_t &v) {
+    bool neg = t[q] == '-';
+    if (neg) ++q;
+    uint64_t m;
+    if (!dec(max_pos + (neg ? 1 : 0), m)) return false;
+    v = neg ? (int64_t)(0 - m) : (int64_t)m;
+    return true;
+  }
+  // hexadecimal with optional 0x, at most `maxd` significant digits
+  TI_D bool hex(int maxd, uint64_t &v) {
+    if (t[q] == '0' && (t[q + 1] | 0x20) == 'x' && !is_end(t[q + 2])) q += 2;
+    uint64_t m = 0;
+    int nsig = 0, ntot = 0;
+    unsigned d;
+    while ((d = hexval(t[q])) < 16) {
+      m = m << 4 | d;
+      if (m) ++nsig;
+      ++ntot; ++q;
+      if (nsig > 16) return false;
+    }
+    v = m;
+    return ntot > 0 && is_end(t[q]) && nsig <= maxd;
+  }
+  TI_D bool reg(unsigned &r) {  // "R<digits>..." as sscanf("R%d") reads it, 0..255
+    if (t[q] != 'R') return false;
+    ++q;
+    unsigned d = t[q] - '0', v = 0;
+    if (d > 9) return false;
+    while ((d = t[q] - '0') <= 9) { v = v * 10 + d; ++q; if (v > 255) return false; }
+    skip_token();
+    r = v;
+    return true;
+  }
+};
+
+// trace_driven.cc:128-149
+TI_HD int oprnd_type_of(unsigned op, unsigned sp) {
+  switch (op) {
+    case OP_SP: case OP_SFU: case OP_SPEC0 + 1: case OP_SPEC0 + 2: case OP_DP: case OP_LOAD: case OP_STORE: return 1;
+    case OP_INTP: case OP_SPEC0 + 3: return 0;
+    case OP_ALU:
+      if (sp == SP_FP || sp == SP_TEX || sp == SP_OTHER) return 1;
+      if (sp == SP_INT) return 0;
+      return -1;
+  }
+  return -1;
+}
+
+// Decodes the instruction line starting at smem offset q0.  Returns TI_EF_* flags.
+// `kind` receives bit0 = has addresses (mem_width > 0).
+TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P, uint32_t chunk_text_base,
+                              ti_inst_rec &r, unsigned &kind) {
+  Reader rd = {text, q0};
+  uint64_t u;
+  kind = 0;
+  r.pc = r.mask = r.opc_off = 0; r.mem_idx = 0xFFFFFFFFu;
+  r.dst = 0; r.src[0] = r.src[1] = r.src[2] = r.src[3] = 0;
+  r.opcode_id = 0; r.op = OP_ALU; r.pack_a = (uint8_t)(SP_OTHER | (0u << 5)); r.pack_b = r.pack_c = 0;
+  r.data_size = r.cycles = 0; r.latency = 0; r.initiation_interval = 0; r.opcode_len = 0;
+
+  if (P.trace_version < 3)  // trace_parser.cc:136-143
+    for (int i = 0; i < 4; ++i) { rd.skip_ws(); if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER; }
+  rd.skip_ws(); if (!rd.hex(8, u)) return TI_EF_BAD_NUMBER;
+  r.pc = (uint32_t)u;
+  rd.skip_ws(); if (!rd.hex(8, u)) return TI_EF_BAD_NUMBER;
+  r.mask = (uint32_t)u;
+  rd.skip_ws(); if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
+  if (u > 1) return TI_EF_TOO_MANY_REGS;
+  const unsigned ndst = (unsigned)u;
+  unsigned rv = 0;
+  if (ndst) { rd.skip_ws(); if (!rd.reg(rv)) return TI_EF_BAD_REG; r.dst = (uint8_t)rv; }
+
+  // ---- opcode token: mnemonic key, first 16 bytes, width / STRONG / GPU modifiers
+  rd.skip_ws();
+  if (rd.peek() == '\n') return TI_EF_TRUNCATED;
+  const int qo = rd.q;
+  uint64_t w0 = 0, w1 = 0, tok8 = 0;
+  int len = 0, dot = -1, tlen = 0;
+  bool alldig = true, restdig = true, firstU = false, wfound = false, wbad = false, strong = false, gpu = false;
+  uint32_t tval = 0, width = 4;
+  int tdig = 0;
+  for (;; ++rd.q) {
+    const unsigned c = rd.peek();
+    const bool end = is_end(c);
+    if (end || c == '.') {
+      if (tlen > 0) {  // token boundary (empty tokens are dropped, trace_parser.cc:56-58)
+        if (!wfound) {
+          const bool num = alldig, unum = firstU && tlen > 1 && restdig;
+          if (num || unum) { wfound = true; wbad = tdig > 9; width = tval / 8; }
+        }
+        if (tlen == 6 && tok8 == pack8("STRONG")) strong = true;
+        if (tlen == 3 && tok8 == pack8("GPU")) gpu = true;
+      }
+      if (end) break;
+      if (dot < 0) dot = len;
+      tlen = 0; tok8 = 0; alldig = restdig = true; firstU = false; tval = 0; tdig = 0;
+    } else {
+      const unsigned d = c - '0';
+      if (tlen == 0) { firstU = c == 'U'; alldig = d <= 9; }
+      else { alldig = alldig && d <= 9; restdig = restdig && d <= 9; }
+      if (d <= 9) { if (tdig < 10) tval = tval * 10 + d; ++tdig; }
+      if (tlen < 8) tok8 |= (uint64_t)c << (8 * tlen);
+      ++tlen;
+    }
+    if (len < 8) w0 |= (uint64_t)c << (8 * len);
+    else if (len < 16) w1 |= (uint64_t)c << (8 * (len - 8));
+    ++len;
+  }
+  if (dot < 0) dot = len;
+  if (len > 255) return TI_EF_LONG_OPCODE;
+  r.opc_off = chunk_text_base + (uint32_t)qo;
+  r.opcode_len = (uint8_t)len;
+
+  rd.skip_ws();
+  if (rd.peek() == '\n') return TI_EF_TRUNCATED;
+  if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
+  if (u > 4) return TI_EF_TOO_MANY_REGS;
+  const unsigned nsrc = (unsigned)u;
+  for (unsigned i = 0; i < nsrc; ++i) { rd.skip_ws(); if (!rd.reg(rv)) return TI_EF_BAD_REG; r.src[i] = (uint8_t)rv; }
+  rd.skip_ws();
+  if (rd.peek() == '\n') return TI_EF_TRUNCATED;
+  if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
+  const bool has_mem = u != 0;
+  unsigned mode = 0;
+  if (has_mem) {
+    if (wbad) return TI_EF_BAD_NUMBER;
+    if (width > 255) return TI_EF_BAD_WIDTH;
+    rd.skip_ws();
+    if (rd.peek() == '\n') return TI_EF_TRUNCATED;
+    if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
+    mode = u > 3 ? 3u : (unsigned)u;
+    kind = 1;
+  }
+
+  // ---- mnemonic -> (opcode id, op_type), trace_driven.cc:188-206
+  if (dot == 0 || dot > TI_ISA_MAX_NAME) return TI_EF_UNKNOWN_OPCODE;
+  const uint64_t klo = dot >= 8 ? w0 : (w0 & ((1ull << (8 * dot)) - 1));
+  const uint32_t khi = dot <= 8 ? 0u : (uint32_t)(w1 & ((1ull << (8 * (dot - 8))) - 1));
+  unsigned id = 0, cat = 0;
+  for (uint32_t h = isa_hash(klo, khi), n = 0; n < (uint32_t)kIsaSlots; ++n, h = (h + 1) & (kIsaSlots - 1)) {
+    const uint4 s = __ldg(reinterpret_cast<const uint4 *>(P.isa) + h);
+    const unsigned sid = s.w & 0xff;
+    if (!sid) break;
+    if (s.x == (uint32_t)klo && s.y == (uint32_t)(klo >> 32) && s.z == khi) { id = sid; cat = (s.w >> 8) & 0xff; break; }
+  }
+  if (!id) return TI_EF_UNKNOWN_OPCODE;
+  unsigned op = cat, sp = __ldg(P.spop + id);
+  const int ot = oprnd_type_of(op, sp);  // before the overrides below (trace_driven.cc:201)
+  if (id == TI_OP_MUFU && w1 == 0 && len == 8) {  // whole-string compares, trace_driven.cc:208-217
+    if (w0 == pack8("MUFU.SIN") || w0 == pack8("MUFU.COS")) sp = SP_SIN;
+    if (w0 == pack8("MUFU.EX2") || w0 == pack8("MUFU.RCP")) sp = SP_EXP;
+    if (w0 == pack8("MUFU.RSQ")) sp = SP_SQRT;
+    if (w0 == pack8("MUFU.LG2")) sp = SP_LOG;
+  }
+  if (id == TI_OP_IMAD && ((len == 8 && w1 == 0 && w0 == pack8("IMAD.MOV")) ||
+                           (len == 9 && w0 == pack8("IMAD.IAD") && w1 == pack8("D"))))
+    sp = SP_INT;                                  // trace_driven.cc:219-222
+  unsigned lat = P.lat[fold_op(cat)][0], init = P.lat[fold_op(cat)][1];  // trace_driven.cc:243
+  unsigned data_size = has_mem ? width : 0, memory_op = 0, space = SPACE_UNDEF, cache_op = CACHE_UNDEF;
+  bool atomic = false, cconst = false, need_w = false, resolve = false;
+  switch (id) {                                   // trace_driven.cc:254-378
+    case TI_OP_LDC: data_size = 4; memory_op = 1; cconst = true; space = SPACE_CONST; cache_op = CACHE_ALL; break;
+    case TI_OP_LDG: case TI_OP_LDL:
+      need_w = true; memory_op = 1; cache_op = (strong && gpu) ? CACHE_GLOBAL : CACHE_ALL;
+      space = id == TI_OP_LDL ? SPACE_LOCAL : SPACE_GLOBAL; break;
+    case TI_OP_STG: case TI_OP_STL:
+      need_w = true; memory_op = 2; cache_op = CACHE_ALL; space = id == TI_OP_STL ? SPACE_LOCAL : SPACE_GLOBAL; break;
+    case TI_OP_ATOMG: case TI_OP_RED: case TI_OP_ATOM:
+      need_w = true; memory_op = 1; op = OP_LOAD; space = SPACE_GLOBAL; atomic = true; cache_op = CACHE_GLOBAL; break;
+    case TI_OP_LDS: need_w = true; memory_op = 1; space = SPACE_SHARED; break;
+    case TI_OP_STS: need_w = true; memory_op = 2; space = SPACE_SHARED; break;
+    case TI_OP_ATOMS: need_w = true; atomic = true; memory_op = 1; space = SPACE_SHARED; break;
+    case TI_OP_LDSM: need_w = true; space = SPACE_SHARED; break;
+    case TI_OP_LD: case TI_OP_ST:
+      need_w = true; memory_op = id == TI_OP_LD ? 1 : 2;
+      if (P.shmem_base == 0 || P.local_base == 0) space = SPACE_SHARED;
+      else resolve = has_mem && r.mask != 0;      // first active address decides (memory phase)
+      break;
+    case TI_OP_HADD2: case TI_OP_HADD2_32I: case TI_OP_HFMA2: case TI_OP_HFMA2_32I: case TI_OP_HMUL2_32I:
+    case TI_OP_HSET2: case TI_OP_HSETP2: init /= 2; break;
+    default: break;
+  }
+  if (need_w && data_size == 0) return TI_EF_ZERO_WIDTH;
+  // a ld/st-class opcode without addresses trips the reference's assert at
+  // abstract_hardware_model.cc:296 as soon as one lane is active
+  if (!has_mem && r.mask && (op == OP_LOAD || op == OP_STORE || op == OP_TLOAD || op == OP_TSTORE)) return TI_EF_UNDEF_SPACE;
+  r.opcode_id = (uint8_t)id; r.op = (uint8_t)op;
+  r.pack_a = (uint8_t)(sp | (unsigned)(ot + 1) << 5);
+  r.pack_b = (uint8_t)(nsrc | ndst << 3 | memory_op << 4 | (atomic ? 1u : 0u) << 6 | (cconst ? 1u : 0u) << 7);
+  r.pack_c = (uint8_t)(space | cache_op << 4 | (has_mem ? 1u : 0u) << 7);
+  r.data_size = (uint8_t)data_size;
+  r.latency = (uint16_t)lat; r.initiation_interval = (uint8_t)init;
+  if (has_mem) r.mem_idx = memtmp_make((unsigned)rd.q, mode, resolve);
+  return 0;
+}
+
+}  // namespace ti
+#endif

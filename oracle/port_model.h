@@ -65,7 +65,8 @@ static inline void convert(const Line &L, const IsaView &isa, const ti_config &c
   std::vector<std::string> toks;
   opcode_tokens(L.opc_b, L.opc_e, toks);
   std::string full(L.opc_b, L.opc_e);
-  auto it = toks.empty() ? isa.by_name.end() : isa.by_name.find(toks[0]);
+  // an opcode that starts with '.' is outside the tracer grammar: flagged, not looked up
+  auto it = (toks.empty() || *L.opc_b == '.') ? isa.by_name.end() : isa.by_name.find(toks[0]);
   if (it == isa.by_name.end()) { I.flags |= TI_EF_UNKNOWN_OPCODE; return; }  // TD:202-206
   I.opcode_id = it->second.first;
   const unsigned cat = it->second.second;

@@ -1,0 +1,131 @@
+"""Parity checks shared by the CPU-emulated (test_emu_kernel.py) and the GPU
+(test_gpu_parity.py) suites.  Bar: bit-exact for records, address rows, transaction
+lists and integer counters; 1e-9 relative for the AccelWattch floating-point sums
+(BASELINE.json north_star)."""
+import glob
+import os
+
+import numpy as np
+
+import edge_cases
+import harness
+import tiformat as T
+from accel_sim_framework_distributed_b200 import _ffi, trace_parser
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+POWER_RTOL = 1e-9
+
+
+def parser_with(tp, over):
+    """A parser with the same library but another ti_config (or tp itself)."""
+    if not over:
+        return tp, False
+    lib_path = tp.lib._name
+    return trace_parser(lib_path=lib_path, config=T.qv100_config(**over)), True
+
+
+def check_against_dump(d, o, offsets, skip_counters=("reserved", "n_begin_tb", "n_end_tb", "text_bytes", "n_warp", "n_mem")):
+    msgs = T.compare(d, o, offsets=offsets, text_a=d.text, names=("cuda", "oracle"))
+    msgs += T.compare_counters(d.counters, o.counters, skip=skip_counters)
+    msgs += T.compare_power(d.power, o.power, rtol=POWER_RTOL)
+    assert not msgs, "\n".join(msgs[:12])
+
+
+def golden_names():
+    return sorted(os.path.basename(p)[:-7] for p in glob.glob(os.path.join(GOLDEN, "*.traceg")))
+
+
+def run_golden(tp, name):
+    """CUDA path vs the reference-produced fixture committed under tests/golden."""
+    over = edge_cases.VALID.get(name, (None, {}))[1]
+    p, own = parser_with(tp, over)
+    try:
+        k = p.parse_kernel_info(os.path.join(GOLDEN, name + ".traceg"))
+        d = k.run()
+        o = T.load_dump(os.path.join(GOLDEN, name + ".tidump"))
+        check_against_dump(d, o, offsets=False)
+        p.kernel_finalizer(k)
+    finally:
+        if own:
+            p.close()
+
+
+def run_generated(tp, tmp_path, over=None, **gen):
+    """CUDA path vs the oracle run here on a freshly generated corpus."""
+    p, own = parser_with(tp, over or {})
+    try:
+        path = os.path.join(str(tmp_path), "kernel-1.traceg")
+        harness.generate(path, **gen)
+        k = p.parse_kernel_info(path)
+        d = k.run()
+        cfg = T.qv100_config(**over) if over else None
+        o = T.load_dump(harness.oracle_dump(path, str(tmp_path), config=cfg))
+        check_against_dump(d, o, offsets=harness.oracle_kind() == "port")
+        p.kernel_finalizer(k)
+        return d
+    finally:
+        if own:
+            p.close()
+
+
+def run_error(tp, tmp_path, name):
+    img, flag = edge_cases.ERRORS[name]
+    path = os.path.join(str(tmp_path), name + ".traceg")
+    open(path, "wb").write(img)
+    k = tp.parse_kernel_info(path)
+    k.upload()
+    k.decode()
+    counts = _ffi.Counts()
+    st = tp.lib.ti_kernel_sync(k._h, counts)
+    tp.kernel_finalizer(k)
+    assert st == _ffi.TI_ERR_PARSE, (name, st)
+    assert counts.error_flags & _ffi.EF[flag], (name, hex(counts.error_flags))
+    # the restatement raises the same flag
+    assert harness.oracle_flags(path, str(tmp_path)) & _ffi.EF[flag], name
+
+
+def run_sharded(tp, tmp_path, n_shards, **gen):
+    """Decoding byte-range shards cut at #BEGIN_TB and concatenating the results equals
+    decoding the file in one piece (the path shards with no exchange)."""
+    path = os.path.join(str(tmp_path), "kernel-1.traceg")
+    harness.generate(path, **gen)
+    k = tp.parse_kernel_info(path)
+    whole = k.run()
+    want = dict(inst=whole.inst.copy(), rows=whole.rows.copy(), txn=whole.txn.copy(), tb=whole.tb.copy(),
+                warp=whole.warp.copy(), counters=whole.counters.copy())
+    body = np.fromfile(path, dtype=np.uint8)[k.hdr.body_offset:]
+    cuts = tp.plan_shards(body, n_shards)
+    assert cuts[0] == 0 and cuts[-1] == len(body) and cuts == sorted(cuts)
+    acc = np.zeros(1, dtype=T.COUNTERS)
+    parts = []
+    for b, e in zip(cuts[:-1], cuts[1:]):
+        assert b == 0 or b == e or bytes(body[b:b + 9]) == b"#BEGIN_TB"
+        d = k.run(b, e)
+        cnt = np.zeros(1, dtype=T.COUNTERS)
+        cnt[0] = d.counters
+        tp.lib.ti_counters_add(acc.ctypes.data, cnt.ctypes.data)
+        inst = d.inst.copy()
+        inst["opc_off"] += np.uint32(b)                    # shard-relative -> body-relative
+        parts.append((inst, d.rows.copy(), d.txn.copy(), d.tb.copy(), d.warp.copy()))
+    inst = np.concatenate([p[0] for p in parts])
+    mem_base = np.cumsum([0] + [len(p[1]) for p in parts])
+    inst_base = np.cumsum([0] + [len(p[0]) for p in parts])
+    warp_base = np.cumsum([0] + [len(p[4]) for p in parts])
+    lo = 0
+    for i, p in enumerate(parts):
+        seg = inst[lo:lo + len(p[0])]
+        has = seg["mem_idx"] != 0xFFFFFFFF
+        seg["mem_idx"][has] += np.uint32(mem_base[i])
+        p[3]["first_inst"] += np.uint32(inst_base[i]); p[3]["first_warp"] += np.uint32(warp_base[i])
+        p[3]["text_off"] += np.uint64(cuts[i])
+        p[4]["first_inst"] += np.uint32(inst_base[i])
+        lo += len(p[0])
+    assert np.array_equal(inst, want["inst"])
+    assert np.array_equal(np.concatenate([p[1] for p in parts]), want["rows"])
+    assert np.array_equal(np.concatenate([p[2] for p in parts]), want["txn"])
+    assert np.array_equal(np.concatenate([p[3] for p in parts]), want["tb"])
+    assert np.array_equal(np.concatenate([p[4] for p in parts]), want["warp"])
+    for f in T.COUNTERS.names:
+        if f not in ("reserved",):
+            assert np.array_equal(acc[0][f], want["counters"][f]), f
+    tp.kernel_finalizer(k)

@@ -1,0 +1,31 @@
+"""CPU-only: the SAME kernel source (csrc/*.cuh) compiled with g++ against the
+lock-step SIMT emulator in tests/simt_emu, checked against the oracle.  This is test
+infrastructure for debugging kernel logic without a GPU -- the product never loads
+it; the parity tests proper are tests/test_gpu_parity.py (-m gpu)."""
+import pytest
+
+import edge_cases
+import parity_cases
+
+
+@pytest.mark.parametrize("name", parity_cases.golden_names())
+def test_emu_golden(emu_parser, name):
+    parity_cases.run_golden(emu_parser, name)
+
+
+@pytest.mark.parametrize("profile,kw", [
+    (2, dict(n_tb=12, insts_per_warp=25)),                      # several chunks, look-back across CTAs
+    (3, dict(n_tb=3, insts_per_warp=12, block_threads=64)),     # 32 sectors per instruction
+    (5, dict(n_tb=16, insts_per_warp=10, block_threads=128, binary_version=86)),
+])
+def test_emu_generated(emu_parser, tmp_path, profile, kw):
+    parity_cases.run_generated(emu_parser, tmp_path, profile=profile, seed=40 + profile, **kw)
+
+
+@pytest.mark.parametrize("name", sorted(edge_cases.ERRORS))
+def test_emu_errors(emu_parser, tmp_path, name):
+    parity_cases.run_error(emu_parser, tmp_path, name)
+
+
+def test_emu_sharded(emu_parser, tmp_path):
+    parity_cases.run_sharded(emu_parser, tmp_path, 3, profile=5, seed=9, n_tb=12, insts_per_warp=8, block_threads=96)

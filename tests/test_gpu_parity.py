@@ -1,0 +1,119 @@
+"""GPU parity tests: the CUDA library, called through its C ABI, against the CPU
+oracle (the reference-built oracle/_ref when it travelled with the repo, else the
+port) and against the reference-produced fixtures in tests/golden."""
+import itertools
+import os
+
+import numpy as np
+import pytest
+
+import edge_cases
+import harness
+import parity_cases
+import tiformat as T
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", parity_cases.golden_names())
+def test_golden(cuda_parser, name):
+    parity_cases.run_golden(cuda_parser, name)
+
+
+@pytest.mark.parametrize("profile,kw", [
+    (1, dict(n_tb=64, insts_per_warp=40, grid=(1, 64, 1), block=(16, 16, 1))),
+    (1, dict(n_tb=64, insts_per_warp=40, grid=(1, 64, 1), block=(16, 16, 1), variant=1)),
+    (2, dict(n_tb=2000, insts_per_warp=25)),
+    (3, dict(n_tb=300, insts_per_warp=20)),
+    (4, dict(n_tb=128, insts_per_warp=32, binary_version=80)),
+    (6, dict(n_tb=1, insts_per_warp=5, binary_version=80)),
+])
+def test_generated_profiles(cuda_parser, tmp_path, profile, kw):
+    parity_cases.run_generated(cuda_parser, tmp_path, profile=profile, seed=profile, **kw)
+
+
+CFGS = {
+    "qv100": {},
+    "fermi": dict(coalesce_arch=20),
+    "fermi_skip_l1": dict(coalesce_arch=20, gmem_skip_L1D=1),
+    "parts2_bcast": dict(mem_warp_parts=2, shmem_limited_broadcast=1, num_shmem_bank=16, clock_gated_lanes=0, num_dp_units=0),
+    "arch13_parts4": dict(coalesce_arch=13, mem_warp_parts=4, clock_gated_lanes=0),
+}
+
+
+@pytest.mark.parametrize("cfg,bv", list(itertools.product(CFGS, [35, 61, 70, 75, 86])))
+def test_soup_all_architectures_and_configs(cuda_parser, tmp_path, cfg, bv):
+    parity_cases.run_generated(cuda_parser, tmp_path, over=CFGS[cfg], profile=5, seed=7000 + bv, n_tb=200,
+                               insts_per_warp=12, binary_version=bv, block_threads=128)
+
+
+def test_soup_trace_version_2(cuda_parser, tmp_path):
+    parity_cases.run_generated(cuda_parser, tmp_path, profile=5, seed=77, n_tb=100, insts_per_warp=12, trace_version=2)
+
+
+@pytest.mark.parametrize("name", sorted(edge_cases.ERRORS))
+def test_malformed_lines_are_flagged(cuda_parser, tmp_path, name):
+    parity_cases.run_error(cuda_parser, tmp_path, name)
+
+
+@pytest.mark.parametrize("n_shards", [2, 5])
+def test_byte_range_shards(cuda_parser, tmp_path, n_shards):
+    parity_cases.run_sharded(cuda_parser, tmp_path, n_shards, profile=5, seed=13, n_tb=300, insts_per_warp=10, block_threads=128)
+
+
+def test_staging_overflow_and_capacity_retry(cuda_parser, tmp_path):
+    """Stride-128 accesses give 32 sectors per instruction from 45-byte lines: more
+    transactions per chunk than the smem staging area and than the default output
+    capacity -- exercises the recompute path and the exact-size re-decode."""
+    lines = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (16 * i, 0x7F0000000000 + 4096 * i) for i in range(400)]
+    img = edge_cases.image([(b, 0, 0, [lines] * 4) for b in range(8)])
+    path = os.path.join(str(tmp_path), "k.traceg")
+    open(path, "wb").write(img)
+    k = cuda_parser.parse_kernel_info(path)
+    d = k.run()
+    assert len(d.txn) == 32 * len(d.inst) == 32 * 400 * 4 * 8
+    o = T.load_dump(harness.oracle_dump(path, str(tmp_path)))
+    parity_cases.check_against_dump(d, o, offsets=harness.oracle_kind() == "port")
+    cuda_parser.kernel_finalizer(k)
+
+
+def test_full_size_properties(cuda_parser):
+    """Size-independent properties on a corpus too large for the CPU oracle to check in
+    seconds (256 MB of config-2 text): determinism, CSR consistency, framing, counter
+    identities, and decode -> re-encode round trip of the address rows."""
+    img = harness.generate_bytes(profile=2, seed=2, n_tb=25000, insts_per_warp=25)
+    hdr = cuda_parser.parse_header(img[:4096])
+    body = img[hdr.body_offset:]
+    k = cuda_parser.open_buffer(body, hdr)
+    d = k.run()
+    n_inst = 25000 * 8 * 25
+    assert len(d.inst) == n_inst and len(d.tb) == 25000 and len(d.warp) == 200000
+    c = d.counters
+    assert int(c["hist"].sum()) == n_inst == int(c["op_count"].sum()) == int(c["n_inst"])
+    assert int(c["n_begin_tb"]) == int(c["n_end_tb"]) == 25000
+    # CSR offsets are monotone and end at n_txn; every record points at its own row
+    off = d.txn_off.astype(np.int64)
+    assert off[0] == 0 and off[-1] == len(d.txn) and np.all(np.diff(off) >= 0)
+    has = d.inst["mem_idx"] != 0xFFFFFFFF
+    assert np.array_equal(d.inst["mem_idx"][has], np.arange(int(has.sum()), dtype=np.uint32))
+    # warp headers tile the instruction array
+    assert np.array_equal(d.warp["first_inst"], np.arange(200000, dtype=np.uint32) * 25)
+    # every transaction of this corpus is one 32 B sector covering lanes that hit it
+    assert np.all(d.txn["size"] == 32) and np.all(d.txn["addr"] % 32 == 0)
+    rows = d.rows
+    mask = d.inst["mask"][has]
+    act = ((mask[:, None] >> np.arange(32, dtype=np.uint32)) & 1).astype(bool)
+    # round trip: base + 4 * lane for active lanes of the first run, 0 elsewhere (generator's rule)
+    base = rows[np.arange(len(rows)), act.argmax(axis=1)]
+    lane0 = act.argmax(axis=1)
+    want = np.where(act, base[:, None] + 4 * (np.arange(32)[None, :] - lane0[:, None]).astype(np.int64).astype(np.uint64), 0)
+    assert np.array_equal(rows[act.any(axis=1)], want[act.any(axis=1)])
+    # lanes of a row's transactions partition its active, non-zero lanes
+    cnt = np.diff(off)
+    lanes = np.bitwise_or.reduceat(d.txn["lane_mask"], off[:-1][cnt > 0]) if len(d.txn) else np.array([])
+    assert np.array_equal(lanes, mask[cnt > 0])
+    # determinism: a second decode is bit-identical
+    inst1, txn1 = d.inst.copy(), d.txn.copy()
+    d2 = k.run()
+    assert np.array_equal(inst1, d2.inst) and np.array_equal(txn1, d2.txn)
+    cuda_parser.kernel_finalizer(k)
