@@ -250,6 +250,7 @@ void ti_kernel_close(ti_kernel *k) {
 }
 
 ti_status ti_kernel_upload(ti_kernel *k, size_t begin, size_t end) {
+  if (k && end == (size_t)-1) end = k->body_len;
   if (!k || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
   if (end - begin > 0xfffffff0ull) { ti::set_error("shard of %zu bytes: cut it with ti_plan_shards", end - begin); return TI_ERR_TOO_LARGE; }
   k->decoded = k->synced = k->retried = false;

@@ -26,6 +26,8 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
   uint16_t *inst_off = reinterpret_cast<uint16_t *>(smem + oInstOff);
   uint16_t *sl_off = reinterpret_cast<uint16_t *>(smem + oSlOff);
   uint16_t *mem_list = reinterpret_cast<uint16_t *>(smem + oMemList);
+  uint16_t *fast_list = reinterpret_cast<uint16_t *>(smem + oFastList);
+  uint16_t *slow_list = reinterpret_cast<uint16_t *>(smem + oSlowList);
   uint16_t *txn_slot = reinterpret_cast<uint16_t *>(smem + oTxnSlot);
   uint16_t *txn_loc = reinterpret_cast<uint16_t *>(smem + oTxnLoc);
   uint8_t *txn_cnt = smem + oTxnCnt;
@@ -44,7 +46,7 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
     __syncthreads();  // previous chunk fully drained (also orders the counter init)
     if (tid == 0) {
       ms->chunk = atomicAdd(&P.g->ticket, 1u);
-      ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0;
+      ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
     }
     __syncthreads();
     const uint32_t chunk = ms->chunk;
@@ -146,9 +148,18 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
     __syncthreads();
 
     // ---------------------------------------------------------------- P3 memory-instruction ordinals
-    const uint32_t n_mem = block_scan(
-        n_inst, ms->warp_tot, [&](uint32_t i) { return (uint32_t)(kind[i] & 1); },
-        [&](uint32_t i, uint32_t ex, uint32_t v) { if (v) mem_list[ex] = (uint16_t)i; });
+    // low half: all memory instructions; high half: those taking the thread-per-instruction path
+    const bool stride_path = P.mem_warp_parts == 1;
+    const uint32_t p3 = block_scan(
+        n_inst, ms->warp_tot,
+        [&](uint32_t i) { const unsigned kd = kind[i]; return (uint32_t)((kd & 1) | ((stride_path && (kd & 2)) ? 0x10000u : 0u)); },
+        [&](uint32_t i, uint32_t ex, uint32_t v) {
+          if (!v) return;
+          const uint32_t mo = ex & 0xffff, fo = ex >> 16;
+          mem_list[mo] = (uint16_t)i;
+          if (v >> 16) fast_list[fo] = (uint16_t)mo; else slow_list[mo - fo] = (uint16_t)mo;
+        });
+    const uint32_t n_mem = p3 & 0xffff, n_fast = p3 >> 16, n_slow = n_mem - n_fast;
 
     // ---------------------------------------------------------------- P4 look-back #1
     if (wid == 0) {
@@ -216,12 +227,47 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
           note_error(ms, fl, tbase + (uint32_t)o);
         });
 
-    // ---------------------------------------------------------------- P6 memory phase
+    // ---------------------------------------------------------------- P6a base+stride: thread per instruction
+    for (uint32_t fo = tid; fo < n_fast; fo += kThreads) {
+      const uint32_t mo = fast_list[fo];
+      ti_inst_rec *rp = recs + mem_list[mo];
+      const uint32_t mask = rp->mask, tmp = rp->mem_idx;
+      const unsigned ds = rp->data_size, op = rp->op;
+      StrideDesc d;
+      uint32_t fl = 0;
+      if (!stride_parse(text, tmp & 0xffff, mask, ds ? ds : 1, d, fl)) {
+        slow_list[n_slow + atomicAdd(&ms->n_extra, 1u)] = (uint16_t)mo;  // wraps around 2^64: not monotone
+        continue;
+      }
+      const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
+      if (!fl && mask && !seg) fl = TI_EF_BAD_WIDTH;
+      if (fl) { note_error(ms, fl, rp->opc_off); if (fl & TI_EF_BAD_NUMBER) d.n = 0; }
+      const uint64_t row = base_mem + mo;
+      if (row < P.cap_mem) {
+        ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(P.rows + row * 32);
+#pragma unroll 4
+        for (unsigned l = 0; l < 32; l += 2) dst[l >> 1] = make_ulonglong2(stride_addr(d, l), stride_addr(d, l + 1));
+      }
+      const unsigned n_txn = (fl || !mask) ? 0u : stride_count(d, ds, seg);
+      uint32_t slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
+      if (slot + n_txn > (uint32_t)kTxnStage) slot = 0xFFFFu;
+      txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
+      rp->mem_idx = (uint32_t)row;
+      if (n_txn && slot != 0xFFFFu) {
+        const unsigned is_write = op == OP_STORE ? 1u : 0u;
+        stride_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
+      }
+    }
+    __syncthreads();
+    const uint32_t n_warp_path = n_slow + ms->n_extra;
+
+    // ---------------------------------------------------------------- P6b everything else: warp per instruction
     for (;;) {
-      uint32_t mo = 0;
-      if (lane == 0) mo = atomicAdd(&ms->next_mem, 1u);
-      mo = __shfl_sync(kFull, mo, 0);
-      if (mo >= n_mem) break;
+      uint32_t so = 0;
+      if (lane == 0) so = atomicAdd(&ms->next_mem, 1u);
+      so = __shfl_sync(kFull, so, 0);
+      if (so >= n_warp_path) break;
+      const uint32_t mo = slow_list[so];
       const uint32_t io = mem_list[mo];
       ti_inst_rec *rp = recs + io;
       const uint32_t mask = rp->mask, tmp = rp->mem_idx;

@@ -36,7 +36,7 @@ struct Misc {
   uint64_t base_inst, base_mem, base_tb, base_warp, base_txn;
   uint64_t warp_tot[kWarps];
   uint32_t chunk, n_inst, n_sl, n_mem, n_tb, n_warp, n_txn;
-  uint32_t next_mem, stage_used, err, first_err;
+  uint32_t next_mem, stage_used, err, first_err, n_extra;
 };
 constexpr int align16(int x) { return (x + 15) & ~15; }
 constexpr int oText = 0;
@@ -45,7 +45,9 @@ constexpr int oStage = oRecs + kRecCap * 32;
 constexpr int oInstOff = oStage + kTxnStage * 32;            // u16[kRecCap]  smem offset of each instruction line
 constexpr int oSlOff = oInstOff + align16(kRecCap * 2);      // u16[kSlCap]   smem offset of each structural line
 constexpr int oMemList = oSlOff + align16(kSlCap * 2);       // u16[kRecCap]  record index of each memory instruction
-constexpr int oTxnSlot = oMemList + align16(kRecCap * 2);    // u16[kRecCap]  staging slot (0xFFFF = recompute later)
+constexpr int oFastList = oMemList + align16(kRecCap * 2);   // u16[kRecCap]  memory ordinals taking the thread-per-instruction path
+constexpr int oSlowList = oFastList + align16(kRecCap * 2);  // u16[kRecCap]  memory ordinals taking the warp-per-instruction path
+constexpr int oTxnSlot = oSlowList + align16(kRecCap * 2);   // u16[kRecCap]  staging slot (0xFFFF = recompute later)
 constexpr int oTxnLoc = oTxnSlot + align16(kRecCap * 2);     // u16[kRecCap]  exclusive txn offset inside the chunk
 constexpr int oTxnCnt = oTxnLoc + align16(kRecCap * 2);      // u8 [kRecCap]
 constexpr int oKind = oTxnCnt + align16(kRecCap);            // u8 [kRecCap]  bit0 = has addresses

@@ -140,6 +140,113 @@ TI_D uint64_t decode_addresses(const uint8_t *text, unsigned q, unsigned mode, u
   return active ? sum : 0;
 }
 
+// =====================================================================================
+// Thread-per-instruction path for base+stride lines (the tracer's format for every
+// regular access, tracer_tool.cu:599-636).  The addresses of the first contiguous run
+// of active lanes are an arithmetic progression, so one thread can walk them in
+// ascending order and keep at most two open transactions (the block of the current
+// address and, for a straddling access, the next one): no sort, no cross-lane traffic,
+// 32 instructions per warp in flight instead of one.
+// =====================================================================================
+struct StrideDesc {
+  uint64_t base;
+  int64_t stride;
+  unsigned first, n;  // lanes [first, first + n) carry base + i * stride; every other lane reads 0
+};
+
+// Parses "0x<base> <stride>" at smem offset q.  Returns false when the progression wraps
+// around 2^64 (then it is not monotone and the warp path handles the instruction).
+TI_D bool stride_parse(const uint8_t *text, unsigned q, uint32_t mask, unsigned ds, StrideDesc &d, uint32_t &flags) {
+  Reader rd = {text, (int)q};
+  d.base = 0; d.stride = 0; d.first = 0; d.n = 0;
+  rd.skip_ws();
+  if (rd.peek() != '\n') {
+    if (!rd.hex(16, d.base)) { flags |= TI_EF_BAD_NUMBER; return true; }
+    rd.skip_ws();
+    if (rd.peek() != '\n' && !rd.sdec(0x7fffffffull, d.stride)) { flags |= TI_EF_BAD_NUMBER; return true; }
+  }
+  if (!mask) return true;
+  d.first = __ffs(mask) - 1;
+  const uint32_t inv = ~(mask >> d.first);
+  d.n = inv ? __ffs(inv) - 1 : 32;
+  const uint64_t span = (uint64_t)(d.stride < 0 ? -d.stride : d.stride) * (d.n - 1);
+  if (d.stride >= 0) return d.base + span + (ds - 1) >= d.base;  // no overflow past 2^64
+  return d.base >= span && d.base + (ds - 1) >= d.base;
+}
+
+TI_D uint64_t stride_addr(const StrideDesc &d, unsigned lane) {
+  return lane >= d.first && lane < d.first + d.n ? d.base + (uint64_t)d.stride * (uint64_t)(lane - d.first) : 0;
+}
+
+// number of transactions: distinct blocks over all touches, visited in ascending order
+TI_D unsigned stride_count(const StrideDesc &d, unsigned ds, unsigned seg) {
+  const uint64_t segmask = ~(uint64_t)(seg - 1);
+  unsigned cnt = 0;
+  uint64_t hi = 0;
+  bool any = false;
+  for (unsigned k = 0; k < d.n; ++k) {
+    const unsigned i = d.stride >= 0 ? k : d.n - 1 - k;
+    const uint64_t a = d.base + (uint64_t)d.stride * i;
+    if (a == 0) continue;                                // abstract_hardware_model.cc:534-537
+    const uint64_t A = a & segmask, B = (a + ds - 1) & segmask;
+    if (!any || A > hi) { ++cnt; hi = A; any = true; }
+    if (B > hi) { ++cnt; hi = B; }
+  }
+  return cnt;
+}
+
+struct OpenTxn { uint32_t lanes, b0, b1, b2, b3, chunks; };
+TI_D void open_clear(OpenTxn &t) { t.lanes = t.b0 = t.b1 = t.b2 = t.b3 = t.chunks = 0; }
+TI_D void open_touch(OpenTxn &t, uint64_t a, unsigned ds, unsigned lane) {
+  const unsigned idx = (unsigned)(a & 127), k = idx >> 5;
+  const uint64_t v = (uint64_t)((1u << ds) - 1) << (idx & 31);
+  const uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+  t.b0 |= k == 0 ? lo : 0u;
+  t.b1 |= (k == 1 ? lo : 0u) | (k == 0 ? hi : 0u);
+  t.b2 |= (k == 2 ? lo : 0u) | (k == 1 ? hi : 0u);
+  t.b3 |= (k == 3 ? lo : 0u) | (k == 2 ? hi : 0u);
+  t.chunks |= 1u << k;
+  t.lanes |= 1u << lane;
+}
+TI_D void open_flush(const OpenTxn &t, uint64_t block, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out, unsigned &n) {
+  if (!t.lanes) return;
+  Txn x;
+  x.block = block; x.lanes = t.lanes; x.bytes[0] = t.b0; x.bytes[1] = t.b1; x.bytes[2] = t.b2; x.bytes[3] = t.b3; x.chunks = t.chunks;
+  const ti_txn_rec r = reduce_and_send(x, seg, type, is_write);
+  const uint4 *src = reinterpret_cast<const uint4 *>(&r);
+  uint4 *dst = reinterpret_cast<uint4 *>(out + n);
+  dst[0] = src[0]; dst[1] = src[1];
+  ++n;
+}
+
+// writes the transactions in ascending block order (the std::map order of
+// abstract_hardware_model.cc:576-584); returns how many
+TI_D unsigned stride_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out) {
+  const uint64_t segmask = ~(uint64_t)(seg - 1);
+  OpenTxn c0, c1;             // blocks b and b + seg
+  open_clear(c0); open_clear(c1);
+  uint64_t b = 0;
+  unsigned n = 0;
+  for (unsigned k = 0; k < d.n; ++k) {
+    const unsigned i = d.stride >= 0 ? k : d.n - 1 - k;
+    const uint64_t a = d.base + (uint64_t)d.stride * i;
+    if (a == 0) continue;
+    const uint64_t A = a & segmask, last = a + ds - 1;
+    if (A != b) {               // every later touch is >= A: close what lies below it
+      open_flush(c0, b, seg, type, is_write, out, n);
+      if (A == b + seg) { c0 = c1; }
+      else { open_flush(c1, b + seg, seg, type, is_write, out, n); open_clear(c0); }
+      open_clear(c1);
+      b = A;
+    }
+    open_touch(c0, a, ds, d.first + i);
+    if ((last & segmask) != A) open_touch(c1, last, ds, d.first + i);   // the straddle rule, :559-571
+  }
+  open_flush(c0, b, seg, type, is_write, out, n);
+  open_flush(c1, b + seg, seg, type, is_write, out, n);
+  return n;
+}
+
 // ---- shared-memory bank conflicts: returns `cycles` (warp-uniform)
 TI_D unsigned shared_cycles(const DecodeParams &P, uint32_t mask, uint64_t addr) {
   const unsigned lane = lane_id();

@@ -120,7 +120,7 @@ TI_HD int oprnd_type_of(unsigned op, unsigned sp) {
 }
 
 // Decodes the instruction line starting at smem offset q0.  Returns TI_EF_* flags.
-// `kind` receives bit0 = has addresses (mem_width > 0).
+// `kind` receives bit0 = has addresses (mem_width > 0), bit1 = eligible for the stride path.
 TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P, uint32_t chunk_text_base,
                               ti_inst_rec &r, unsigned &kind) {
   Reader rd = {text, q0};
@@ -264,6 +264,8 @@ TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P
   r.data_size = (uint8_t)data_size;
   r.latency = (uint16_t)lat; r.initiation_interval = (uint8_t)init;
   if (has_mem) r.mem_idx = memtmp_make((unsigned)rd.q, mode, resolve);
+  // base+stride global loads/stores take the thread-per-instruction path (ti_mem.cuh)
+  if (has_mem && mode == 1 && space == SPACE_GLOBAL && !atomic && (op == OP_LOAD || op == OP_STORE)) kind |= 2;
   return 0;
 }
 
