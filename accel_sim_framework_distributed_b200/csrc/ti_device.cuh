@@ -33,14 +33,23 @@
 namespace ti {
 
 // ------------------------------------------------------------------ tunables
-constexpr int kChunk = 16384;           // bytes of text owned by one chunk
-constexpr int kThreads = 256;           // threads per CTA
+#ifndef TI_CHUNK
+#define TI_CHUNK 16384
+#endif
+#ifndef TI_THREADS
+#define TI_THREADS 256
+#endif
+#ifndef TI_TXN_STAGE
+#define TI_TXN_STAGE 1024
+#endif
+constexpr int kChunk = TI_CHUNK;        // bytes of text owned by one chunk
+constexpr int kThreads = TI_THREADS;    // threads per CTA
 constexpr int kWarps = kThreads / 32;
 constexpr int kSlack = TI_MAX_LINE;     // bytes loaded past the chunk so its last line is complete
 constexpr int kTextBytes = 16 + kChunk + kSlack + 48;  // 16 B before the chunk, 48 B of '\n' sentinel after
 constexpr int kRecCap = kChunk / 24;    // no tracer line is shorter than 24 bytes with its '\n'
 constexpr int kSlCap = kChunk / 8 + 1;  // "#END_TB\n": no valid non-blank line is shorter than 8
-constexpr int kTxnStage = 1024;         // transactions staged in smem per chunk before look-back #2
+constexpr int kTxnStage = TI_TXN_STAGE; // transactions staged in smem per chunk before look-back #2
 constexpr int kFlushEvery = 64;         // chunks between counter flushes
 
 // -------------------------------------------------------------- enum values

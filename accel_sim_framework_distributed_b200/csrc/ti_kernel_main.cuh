@@ -19,8 +19,6 @@ TI_D void flush_counters(uint32_t *cnt, unsigned long long *g) {
 
 __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams P) {
   TI_DYN_SMEM(smem);
-  uint8_t *text = smem + oText;
-  uint4 *text_v = reinterpret_cast<uint4 *>(smem + oText);
   ti_inst_rec *recs = reinterpret_cast<ti_inst_rec *>(smem + oRecs);
   ti_txn_rec *stage = reinterpret_cast<ti_txn_rec *>(smem + oStage);
   uint16_t *inst_off = reinterpret_cast<uint16_t *>(smem + oInstOff);
@@ -42,34 +40,75 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
   for (int i = tid; i < kSmCnt; i += kThreads) cnt[i] = 0;
   unsigned done_chunks = 0;
 
-  for (;;) {
-    __syncthreads();  // previous chunk fully drained (also orders the counter init)
+  // ---- stage-in helpers.  Buffer offset j holds text byte (chunk * kChunk - 16 + j).  The
+  // part of [0, 16 + kChunk + kSlack) that lies inside the shard on 16 B boundaries comes by
+  // one TMA bulk copy (issued by one thread); the rest -- the virtual '\n' before the shard,
+  // the tail past its end, a last partial vector, the sentinel -- is filled by all threads.
+  auto bulk_range = [&](uint32_t c, uint32_t &v_lo, uint32_t &v_hi) {  // vector range of the bulk copy
+    const uint64_t cb = (uint64_t)c * kChunk;
+    v_lo = c == 0 ? 1u : 0u;
+    const uint64_t full = P.len / 16;                                   // whole vectors of the shard
+    const uint64_t first = cb / 16 - (c == 0 ? 0 : 1);                  // text vector held by buffer vector v_lo
+    const uint64_t avail = full > first ? full - first : 0;
+    const uint64_t want = (uint64_t)(16 + kChunk + kSlack) / 16 - v_lo;
+    v_hi = v_lo + (uint32_t)(avail < want ? avail : want);
+  };
+  auto issue_bulk = [&](uint32_t c, unsigned buf) {                     // one thread
+    uint32_t v_lo, v_hi;
+    bulk_range(c, v_lo, v_hi);
+    uint8_t *dst = smem + oText + buf * kTextBytes;
+    const unsigned bytes = (v_hi - v_lo) * 16;
+    fence_proxy_async();                       // the buffer was last touched through the generic proxy
+    mbar_expect_tx(&ms->mbar[buf], bytes);
+    if (bytes) bulk_g2s(dst + v_lo * 16, P.text + ((uint64_t)c * kChunk - 16 + (uint64_t)v_lo * 16), bytes, &ms->mbar[buf]);
+  };
+  auto fill_edges = [&](uint32_t c, unsigned buf) {                     // all threads
+    uint32_t v_lo, v_hi;
+    bulk_range(c, v_lo, v_hi);
+    uint4 *tv = reinterpret_cast<uint4 *>(smem + oText + buf * kTextBytes);
+    const uint64_t cb = (uint64_t)c * kChunk;
+    for (uint32_t v = tid; v < (uint32_t)(kTextBytes / 16); v += kThreads) {
+      if (v >= v_lo && v < v_hi) continue;
+      const int64_t pos = (int64_t)cb - 16 + (int64_t)v * 16;
+      uint32_t w[4] = {0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au};
+      if (v < (uint32_t)((16 + kChunk + kSlack) / 16) && pos >= 0)
+        for (int b = 0; b < 16 && (uint64_t)pos + b < P.len; ++b)   // the shard's last, partial vector
+          w[b >> 2] = (w[b >> 2] & ~(0xffu << (8 * (b & 3)))) | (uint32_t)P.text[pos + b] << (8 * (b & 3));
+      tv[v] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  };
+
+  // prologue: first ticket, first bulk copy
+  if (tid == 0) {
+    mbar_init(&ms->mbar[0], 1);
+    mbar_init(&ms->mbar[1], 1);
+    ms->chunk_next = atomicAdd(&P.g->ticket, 1u);
+    if (ms->chunk_next < P.n_chunks) issue_bulk(ms->chunk_next, 0);
+  }
+  __syncthreads();
+  if (ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, 0);
+
+  for (unsigned iter = 0;; ++iter) {
+    __syncthreads();  // previous chunk fully drained; edge fills of this chunk's buffer visible
+    const unsigned buf = iter & 1;
+    const uint32_t chunk = ms->chunk_next;
+    if (chunk >= P.n_chunks) break;
+    __syncthreads();  // everyone has read chunk_next
     if (tid == 0) {
-      ms->chunk = atomicAdd(&P.g->ticket, 1u);
+      // take the next ticket now and prefetch its text into the other buffer (free since the
+      // barrier above): tickets stay in file order, which is all the look-back needs
+      const uint32_t nxt = atomicAdd(&P.g->ticket, 1u);
+      ms->chunk_next = nxt;
+      if (nxt < P.n_chunks) issue_bulk(nxt, buf ^ 1);
       ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
     }
     __syncthreads();
-    const uint32_t chunk = ms->chunk;
-    if (chunk >= P.n_chunks) break;
+    if (ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, buf ^ 1);
+    uint8_t *text = smem + oText + buf * kTextBytes;
+    uint4 *text_v = reinterpret_cast<uint4 *>(text);
     const uint64_t cb = (uint64_t)chunk * kChunk;            // text offset of the chunk
     const uint32_t tbase = (uint32_t)(cb - 16);              // text offset = tbase + smem offset (mod 2^32)
-
-    // ---------------------------------------------------------------- P0 stage-in
-    for (int v = tid; v < kTextBytes / 16; v += kThreads) {
-      const int64_t pos = (int64_t)cb - 16 + (int64_t)v * 16;
-      uint4 x = make_uint4(0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au);
-      if (v < (16 + kChunk + kSlack) / 16 && pos >= 0 && (uint64_t)pos < P.len) {
-        if ((uint64_t)pos + 16 <= P.len) x = __ldg(reinterpret_cast<const uint4 *>(P.text + pos));
-        else {
-          uint32_t w[4] = {0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au, 0x0a0a0a0au};
-          for (int b = 0; b < 16 && (uint64_t)pos + b < P.len; ++b)
-            w[b >> 2] = (w[b >> 2] & ~(0xffu << (8 * (b & 3)))) | (uint32_t)P.text[pos + b] << (8 * (b & 3));
-          x = make_uint4(w[0], w[1], w[2], w[3]);
-        }
-      }
-      text_v[v] = x;
-    }
-    __syncthreads();
+    mbar_wait(&ms->mbar[buf], (iter >> 1) & 1);              // P0: this chunk's bulk copy has landed
 
     // ---------------------------------------------------------------- P1 line index
     // A line start is a byte that follows '\n' and is not '\n' itself (blank lines
@@ -84,13 +123,14 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
     uint32_t run = 0;
 #pragma unroll
     for (int it = 0; it < kVecIters; ++it) {
-      const uint32_t v = wid * (kVecIters * 32) + it * 32 + lane, s0 = v * 16;
-      const uint32_t m = nl_mask16(text_v[1 + v]);
-      nlmap[1 + v] = (uint16_t)m;
+      const uint32_t v = wid * kVecPerWarp + it * 32 + lane, s0 = v * 16;
+      const bool inside = v < (uint32_t)(kChunk / 16);
+      const uint32_t m = inside ? nl_mask16(text_v[1 + v]) : 0u;
+      if (inside) nlmap[1 + v] = (uint16_t)m;
       const uint32_t up = __shfl_up_sync(kFull, m, 1);
-      const uint32_t prev = lane ? (up >> 15) & 1 : (text[16 + s0 - 1] == '\n');
+      const uint32_t prev = lane ? (up >> 15) & 1 : (inside && text[16 + s0 - 1] == '\n');
       uint32_t st = ((m << 1) | prev) & ~m & 0xffffu;
-      if (s0 >= lim) st = 0;
+      if (!inside || s0 >= lim) st = 0;
       else if (s0 + 16 > lim) st &= (1u << (lim - s0)) - 1;
       uint32_t packed = 0;
       for (uint32_t b = st; b; b &= b - 1) {
@@ -121,7 +161,7 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
     } else {
 #pragma unroll
       for (int it = 0; it < kVecIters; ++it) {
-        const uint32_t s0 = (wid * (kVecIters * 32) + it * 32 + lane) * 16;
+        const uint32_t s0 = (wid * kVecPerWarp + it * 32 + lane) * 16;
         uint32_t at = pbase + excl[it];
         for (uint32_t b = starts[it]; b; b &= b - 1) {
           const uint32_t o = 16 + s0 + __ffs(b) - 1;

@@ -36,11 +36,12 @@ struct Misc {
   uint64_t base_inst, base_mem, base_tb, base_warp, base_txn;
   uint64_t warp_tot[kWarps];
   uint32_t chunk, n_inst, n_sl, n_mem, n_tb, n_warp, n_txn;
-  uint32_t next_mem, stage_used, err, first_err, n_extra;
+  uint32_t next_mem, stage_used, err, first_err, n_extra, chunk_next;
+  uint64_t mbar[2];  // one mbarrier per text buffer (completion of the bulk copy)
 };
 constexpr int align16(int x) { return (x + 15) & ~15; }
-constexpr int oText = 0;
-constexpr int oRecs = oText + kTextBytes;
+constexpr int oText = 0;                                     // two text buffers: the chunk being decoded + the prefetched next one
+constexpr int oRecs = oText + 2 * kTextBytes;
 constexpr int oStage = oRecs + kRecCap * 32;
 constexpr int oInstOff = oStage + kTxnStage * 32;            // u16[kRecCap]  smem offset of each instruction line
 constexpr int oSlOff = oInstOff + align16(kRecCap * 2);      // u16[kSlCap]   smem offset of each structural line
@@ -56,9 +57,44 @@ constexpr int oTok = oCnt + align16(kSmCnt * 4);             // u16[kWarps][34]
 constexpr int oNlMap = oTok + align16(kWarps * 34 * 2);      // u16[kTextBytes/16] newline bitmap of the staged text
 constexpr int oMisc = oNlMap + align16(kTextBytes / 16 * 2 + 4);
 constexpr int kSmemBytes = oMisc + align16((int)sizeof(Misc));
-static_assert(kTextBytes % 16 == 0 && (kChunk / 16) % kThreads == 0, "chunk geometry");
+static_assert(kTextBytes % 16 == 0 && kChunk % 16 == 0 && kThreads % 32 == 0, "chunk geometry");
 static_assert(kTextBytes < 65536, "smem offsets are 16 bit");
-constexpr int kVecIters = kChunk / 16 / kThreads;
+constexpr int kVecPerWarp = ((kChunk / 16 + kWarps - 1) / kWarps + 31) & ~31;  // 16 B vectors of the chunk per warp
+constexpr int kVecIters = kVecPerWarp / 32;
+
+// ---- TMA 1-D bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier, used to prefetch the
+// next chunk's text while the current one is decoded.  Under the emulator the copy is a
+// synchronous memcpy and the barrier a no-op, so the control flow stays identical.
+#ifdef TI_EMU
+TI_D void mbar_init(uint64_t *, unsigned) {}
+TI_D void mbar_expect_tx(uint64_t *, unsigned) {}
+TI_D void bulk_g2s(void *dst, const void *src, unsigned bytes, uint64_t *) { memcpy(dst, src, bytes); }
+TI_D void mbar_wait(uint64_t *, unsigned) {}
+TI_D void fence_proxy_async() {}
+#else
+TI_D uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+TI_D void mbar_init(uint64_t *b, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+TI_D void mbar_expect_tx(uint64_t *b, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+TI_D void bulk_g2s(void *dst, const void *src, unsigned bytes, uint64_t *b) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(b))
+               : "memory");
+}
+TI_D void mbar_wait(uint64_t *b, unsigned parity) {
+  uint32_t ok = 0;
+  while (!ok)
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok)
+                 : "r"(smem_u32(b)), "r"(parity)
+                 : "memory");
+}
+TI_D void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+#endif
 
 TI_D uint32_t ld_flag(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
 TI_D uint32_t ld_vol(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }

@@ -10,7 +10,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GEN = os.path.join(ROOT, "tools", "libtigen.so")
 REF_ORACLE = os.path.join(ROOT, "oracle", "_ref", "ref_oracle")
 PORT_ORACLE = os.path.join(ROOT, "oracle", "port_oracle")
-CUDA_LIB = os.path.join(ROOT, "accel_sim_framework_distributed_b200", "csrc", "libtraceingest.so")
+# TI_LIB: tuning builds of the same CUDA library (bench sweeps only)
+CUDA_LIB = os.environ.get("TI_LIB") or os.path.join(ROOT, "accel_sim_framework_distributed_b200", "csrc", "libtraceingest.so")
 EMU_LIB = os.path.join(ROOT, "tests", "simt_emu", "libtraceingest_emu.so")
 
 
