@@ -33,7 +33,8 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
   uint32_t *cnt = reinterpret_cast<uint32_t *>(smem + oCnt);
   uint16_t *nlmap = reinterpret_cast<uint16_t *>(smem + oNlMap);
   const uint32_t *nlmap32 = reinterpret_cast<const uint32_t *>(smem + oNlMap);
-  uint16_t *tokpos = reinterpret_cast<uint16_t *>(smem + oTok) + (threadIdx.x >> 5) * 34;
+  uint32_t *wscratch = reinterpret_cast<uint32_t *>(smem + oTok + (threadIdx.x >> 5) * kWarpScratch);
+  uint16_t *tokpos = reinterpret_cast<uint16_t *>(wscratch);
   Misc *ms = reinterpret_cast<Misc *>(smem + oMisc);
 
   const unsigned tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -330,7 +331,7 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
       const unsigned space = pack_c & 0xf, cache_op = pack_c >> 4 & 7;
       unsigned n_txn = 0, cycles = 0;
       Txn t2[2];
-      unsigned pos0 = lane, seg = 0;
+      unsigned pos[2] = {~0u, ~0u}, seg = 0;
       const bool gated = (op == OP_LOAD || op == OP_STORE || op == OP_TLOAD || op == OP_TSTORE) && mask != 0;
       const unsigned is_write = (op == OP_STORE || op == OP_TSTORE || (pack_b >> 4 & 3) == 2) ? 1u : 0u;
       if (gated && !fl) {
@@ -338,8 +339,8 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
         else if (space == SPACE_GLOBAL) {
           seg = segment_size(P, ds, cache_op);
           if (!seg) fl |= TI_EF_BAD_WIDTH;
-          else if (pack_b >> 6 & 1) n_txn = coalesce_atomic(P, mask, addr, ds, seg, t2[0], pos0, fl);
-          else n_txn = coalesce_global(P, mask, addr, ds, seg, t2);
+          else if (pack_b >> 6 & 1) n_txn = coalesce_atomic(P, mask, addr, ds, seg, t2[0], pos[0], fl);
+          else n_txn = coalesce_global(P, mask, addr, ds, seg, t2, pos, wscratch);
         } else if (space != SPACE_LOCAL) fl |= TI_EF_UNDEF_SPACE;
       }
       if (fl) n_txn = 0;                              // fl is warp-uniform here
@@ -354,8 +355,8 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
       slot = __shfl_sync(kFull, slot, 0);
       if (slot != 0xFFFFu) {
         const unsigned type = is_write ? 4u : 0u;       // GLOBAL_ACC_W / GLOBAL_ACC_R
-        if (lane < n_txn) stage[slot + pos0] = reduce_and_send(t2[0], seg, type, is_write);
-        if (lane + 32 < n_txn) stage[slot + lane + 32] = reduce_and_send(t2[1], seg, type, is_write);
+        if (pos[0] < n_txn) stage[slot + pos[0]] = reduce_and_send(t2[0], seg, type, is_write);
+        if (pos[1] < n_txn) stage[slot + pos[1]] = reduce_and_send(t2[1], seg, type, is_write);
       }
     }
     __syncthreads();
@@ -405,14 +406,14 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
         const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
         const unsigned is_write = (op == OP_STORE || op == OP_TSTORE || (pack_b >> 4 & 3) == 2) ? 1u : 0u;
         Txn t2[2];
-        unsigned pos0 = lane;
+        unsigned pos[2] = {~0u, ~0u};
         uint32_t fl = 0;
         unsigned m;
-        if (pack_b >> 6 & 1) m = coalesce_atomic(P, rp->mask, addr, ds, seg, t2[0], pos0, fl);
-        else m = coalesce_global(P, rp->mask, addr, ds, seg, t2);
+        if (pack_b >> 6 & 1) m = coalesce_atomic(P, rp->mask, addr, ds, seg, t2[0], pos[0], fl);
+        else m = coalesce_global(P, rp->mask, addr, ds, seg, t2, pos, wscratch);
         const unsigned type = is_write ? 4u : 0u;
-        if (lane < m && at + pos0 < P.cap_txn) P.txn[at + pos0] = reduce_and_send(t2[0], seg, type, is_write);
-        if (lane + 32 < m && at + lane + 32 < P.cap_txn) P.txn[at + lane + 32] = reduce_and_send(t2[1], seg, type, is_write);
+        if (pos[0] < m && at + pos[0] < P.cap_txn) P.txn[at + pos[0]] = reduce_and_send(t2[0], seg, type, is_write);
+        if (pos[1] < m && at + pos[1] < P.cap_txn) P.txn[at + pos[1]] = reduce_and_send(t2[1], seg, type, is_write);
       }
     }
 

@@ -53,8 +53,9 @@ constexpr int oTxnLoc = oTxnSlot + align16(kRecCap * 2);     // u16[kRecCap]  ex
 constexpr int oTxnCnt = oTxnLoc + align16(kRecCap * 2);      // u8 [kRecCap]
 constexpr int oKind = oTxnCnt + align16(kRecCap);            // u8 [kRecCap]  bit0 = has addresses
 constexpr int oCnt = oKind + align16(kRecCap);               // u32[kSmCnt]   counter mirror
-constexpr int oTok = oCnt + align16(kSmCnt * 4);             // u16[kWarps][34]
-constexpr int oNlMap = oTok + align16(kWarps * 34 * 2);      // u16[kTextBytes/16] newline bitmap of the staged text
+constexpr int kWarpScratch = 32 * 6 * 4;                     // per warp: token offsets (decode), then B-group merge slots (coalesce)
+constexpr int oTok = oCnt + align16(kSmCnt * 4);
+constexpr int oNlMap = oTok + kWarps * kWarpScratch;      // u16[kTextBytes/16] newline bitmap of the staged text
 constexpr int oMisc = oNlMap + align16(kTextBytes / 16 * 2 + 4);
 constexpr int kSmemBytes = oMisc + align16((int)sizeof(Misc));
 static_assert(kTextBytes % 16 == 0 && kChunk % 16 == 0 && kThreads % 32 == 0, "chunk geometry");

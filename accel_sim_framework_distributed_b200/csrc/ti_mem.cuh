@@ -290,10 +290,20 @@ TI_D unsigned shared_cycles(const DecodeParams &P, uint32_t mask, uint64_t addr)
   return total;
 }
 
-// ---- global coalescing.  Each lane may end up holding up to two finished
-// transactions (index n lives in lane n % 32, slot n / 32).  Returns the count.
+// ---- global coalescing (non-atomic), sort-free.
+// Every active lane makes one "touch" A = (block of its address) and, when its access
+// crosses into the next segment, a second touch B (abstract_hardware_model.cc:559-571).
+// Transactions = distinct blocks over all touches, emitted in ascending block order
+// (std::map, :511,576-584).  Lanes with equal blocks are grouped with match.any, their
+// byte / chunk masks OR-reduced with redux over the group mask, and each group leader
+// ranks its block by counting the leaders with a smaller one (one shuffle broadcast per
+// leader) -- no serial extraction of minima, so 32 scattered sectors cost about as much
+// as 4.  A B-group whose block some A-group also touches is merged into it through a
+// small per-warp smem scratch; the others ("pure B") are transactions of their own.
+// Outputs: out[0]/pos[0] = this lane's A-group if it leads one, out[1]/pos[1] = its pure
+// B-group; pos = ~0u when absent.  Returns the number of transactions.
 TI_D unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_t addr, unsigned ds, unsigned seg,
-                              Txn out[2]) {
+                              Txn out[2], unsigned pos[2], uint32_t *scratch) {
   const unsigned lane = lane_id();
   const unsigned parts = (unsigned)P.mem_warp_parts, sub = 32 / parts;
   const uint64_t segmask = ~(uint64_t)(seg - 1);
@@ -302,29 +312,71 @@ TI_D unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_t add
   const bool act = (mask >> lane & 1) && addr != 0;      // abstract_hardware_model.cc:534-537
   uint32_t wa[4], wb[4];
   byte_words((unsigned)(addr & 127), ds, wa);
-  byte_words((unsigned)(last & 127), ds, wb);            // the straddle rule, :559-571
+  byte_words((unsigned)(last & 127), ds, wb);
   const unsigned ca = 1u << ((addr & 127) / 32), cb = 1u << ((last & 127) / 32);
+  pos[0] = pos[1] = ~0u;
   unsigned n = 0;
   for (unsigned p = 0; p < parts; ++p) {
     const bool in = sub == 32 || (lane / sub) == p;
-    bool pendA = act && in, pendB = pendA && keyA != keyB;
-    while (__ballot_sync(kFull, pendA || pendB)) {
-      uint64_t km = ~0ull;
-      if (pendA) km = keyA;
-      if (pendB && keyB < km) km = keyB;
-      const uint64_t cur = warp_min_u64(km);             // std::map order: ascending block address
-      const bool hitA = pendA && keyA == cur, hitB = pendB && keyB == cur;
-      Txn t;
-      t.block = cur;
-      t.lanes = __ballot_sync(kFull, hitA || hitB);
+    const bool actp = act && in, stradp = actp && keyA != keyB;
+    const uint32_t mA = __ballot_sync(kFull, actp);
+    if (!mA) continue;                                   // warp-uniform
+    const uint32_t mB = __ballot_sync(kFull, stradp);
+    Txn ta, tb;
+    bool leadA = false, leadB = false;
+    if (actp) {
+      const uint32_t g = __match_any_sync(mA, keyA);
+      leadA = (unsigned)(__ffs(g) - 1) == lane;
+      ta.block = keyA; ta.lanes = g;
 #pragma unroll
-      for (int w = 0; w < 4; ++w) t.bytes[w] = __reduce_or_sync(kFull, (hitA ? wa[w] : 0u) | (hitB ? wb[w] : 0u));
-      t.chunks = __reduce_or_sync(kFull, (hitA ? ca : 0u) | (hitB ? cb : 0u));
-      if (lane == (n & 31)) out[n >> 5] = t;
-      ++n;
-      pendA = pendA && !hitA;
-      pendB = pendB && !hitB;
+      for (int w = 0; w < 4; ++w) ta.bytes[w] = __reduce_or_sync(g, wa[w]);
+      ta.chunks = __reduce_or_sync(g, ca);
     }
+    if (stradp) {
+      const uint32_t g = __match_any_sync(mB, keyB);
+      leadB = (unsigned)(__ffs(g) - 1) == lane;
+      tb.block = keyB; tb.lanes = g;
+#pragma unroll
+      for (int w = 0; w < 4; ++w) tb.bytes[w] = __reduce_or_sync(g, wb[w]);
+      tb.chunks = __reduce_or_sync(g, cb);
+    }
+    const uint32_t LA = __ballot_sync(kFull, leadA);
+    unsigned cntA = 0, cntB = 0;
+    int owner = -1;
+    for (uint32_t m = LA; m; m &= m - 1) {               // broadcast every A-leader's block once
+      const int j = __ffs(m) - 1;
+      const uint64_t kj = __shfl_sync(kFull, keyA, j);
+      cntA += kj < keyA;
+      cntB += kj < keyB;
+      if (leadB && kj == keyB) owner = j;
+    }
+    uint32_t LBp = 0;
+    if (mB) {                                            // warp-uniform
+      const bool pureB = leadB && owner < 0, owned = leadB && owner >= 0;
+      LBp = __ballot_sync(kFull, pureB);
+      for (uint32_t m = LBp; m; m &= m - 1) {
+        const int j = __ffs(m) - 1;
+        const uint64_t kj = __shfl_sync(kFull, keyB, j);
+        cntA += kj < keyA;
+        cntB += kj < keyB;
+      }
+      const uint32_t ownedmask = __reduce_or_sync(kFull, owned ? 1u << owner : 0u);
+      if (ownedmask) {
+        if (owned) {
+          uint32_t *s = scratch + owner * 6;
+          s[0] = tb.bytes[0]; s[1] = tb.bytes[1]; s[2] = tb.bytes[2]; s[3] = tb.bytes[3]; s[4] = tb.chunks; s[5] = tb.lanes;
+        }
+        __syncwarp();
+        if (leadA && (ownedmask >> lane & 1)) {
+          const uint32_t *s = scratch + lane * 6;
+          ta.bytes[0] |= s[0]; ta.bytes[1] |= s[1]; ta.bytes[2] |= s[2]; ta.bytes[3] |= s[3]; ta.chunks |= s[4]; ta.lanes |= s[5];
+        }
+        __syncwarp();
+      }
+      if (pureB) { out[1] = tb; pos[1] = n + cntB; }
+    }
+    if (leadA) { out[0] = ta; pos[0] = n + cntA; }
+    n += __popc(LA) + __popc(LBp);
   }
   return n;
 }
@@ -339,7 +391,7 @@ TI_D unsigned coalesce_atomic(const DecodeParams &P, uint32_t mask, uint64_t add
   const uint64_t segmask = ~(uint64_t)(seg - 1);
   unsigned n = 0;
   mine.block = 0; mine.lanes = 0; mine.chunks = 0; mine.bytes[0] = mine.bytes[1] = mine.bytes[2] = mine.bytes[3] = 0;
-  pos = 0;
+  pos = ~0u;
   for (unsigned p = 0; p < parts; ++p) {
     const unsigned first_of_part = n;
     for (unsigned t = p * sub; t < (p + 1) * sub; ++t) {

@@ -49,7 +49,7 @@ struct Slot {           // one in-flight warp collective, keyed by its member ma
   uint64_t in[32], arg[32], out[32];
 };
 
-struct Warp { Slot slots[8]; };
+struct Warp { Slot slots[40]; };
 
 struct Cta {
   std::vector<unsigned char> smem;

@@ -29,3 +29,22 @@ def test_emu_errors(emu_parser, tmp_path, name):
 
 def test_emu_sharded(emu_parser, tmp_path):
     parity_cases.run_sharded(emu_parser, tmp_path, 3, profile=5, seed=9, n_tb=12, insts_per_warp=8, block_threads=96)
+
+
+def test_emu_staging_overflow_and_capacity_retry(emu_parser, tmp_path):
+    """More transactions per chunk than the smem staging area (recompute path) and than
+    the default output capacity (exact-size re-decode)."""
+    import os
+    import harness
+    import tiformat as T
+    lines = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (16 * i, 0x7F0000000000 + 4096 * i) for i in range(150)]
+    lines += ["%04x ffffffff 0 STG.E.64.SYS 2 R4 R6 8 2 0x%x %s 0" % (0x2000 + 16 * i, 0x7F1000000000 + 8192 * i, " ".join(["260"] * 31)) for i in range(40)]
+    img = edge_cases.image([(b, 0, 0, [lines, lines]) for b in range(2)])
+    path = os.path.join(str(tmp_path), "k.traceg")
+    open(path, "wb").write(img)
+    k = emu_parser.parse_kernel_info(path)
+    d = k.run()
+    assert len(d.txn) > 32 * 150 * 4
+    o = T.load_dump(harness.oracle_dump(path, str(tmp_path)))
+    parity_cases.check_against_dump(d, o, offsets=harness.oracle_kind() == "port")
+    emu_parser.kernel_finalizer(k)
