@@ -56,6 +56,11 @@ TI_HD uint32_t memtmp_make(unsigned q, unsigned mode, bool resolve) {
   return q | (mode > 3 ? 3u : mode) << 16 | (resolve ? 1u : 0u) << 18;
 }
 
+// All loops below have ONE exit and no function returns from inside them: the threads
+// of a warp parse 32 different lines, and a `return` in the middle would make the end
+// of the function the only reconvergence point -- after the first variable-length token
+// every lane would then run alone (measured: 5 of 32 lanes active).  Errors are
+// therefore recorded in a flag and parsing simply continues on the (bounded) text.
 struct Reader {
   const uint8_t *t;
   int q;
@@ -67,17 +72,17 @@ struct Reader {
     int nd = 0;
     uint64_t m = 0;
     unsigned d;
-    while ((d = t[q] - '0') <= 9) { m = m * 10 + d; ++q; if (++nd > 19) return false; }
+    while ((d = t[q] - '0') <= 9 && nd < 20) { m = m * 10 + d; ++q; ++nd; }
     v = m;
-    return nd > 0 && is_end(t[q]) && m <= max;
+    return nd > 0 && nd < 20 && is_end(t[q]) && m <= max;
   }
   TI_D bool sdec(uint64_t max_pos, int64_t &v) {
-    bool neg = t[q] == '-';
-    if (neg) ++q;
+    const bool neg = t[q] == '-';
+    q += neg ? 1 : 0;
     uint64_t m;
-    if (!dec(max_pos + (neg ? 1 : 0), m)) return false;
+    const bool ok = dec(max_pos + (neg ? 1 : 0), m);
     v = neg ? (int64_t)(0 - m) : (int64_t)m;
-    return true;
+    return ok;
   }
   // hexadecimal with optional 0x, at most `maxd` significant digits
   TI_D bool hex(int maxd, uint64_t &v) {
@@ -85,24 +90,23 @@ struct Reader {
     uint64_t m = 0;
     int nsig = 0, ntot = 0;
     unsigned d;
-    while ((d = hexval(t[q])) < 16) {
+    while ((d = hexval(t[q])) < 16 && nsig <= 16) {
       m = m << 4 | d;
-      if (m) ++nsig;
+      nsig += m ? 1 : 0;
       ++ntot; ++q;
-      if (nsig > 16) return false;
     }
     v = m;
     return ntot > 0 && is_end(t[q]) && nsig <= maxd;
   }
   TI_D bool reg(unsigned &r) {  // "R<digits>..." as sscanf("R%d") reads it, 0..255
-    if (t[q] != 'R') return false;
-    ++q;
-    unsigned d = t[q] - '0', v = 0;
-    if (d > 9) return false;
-    while ((d = t[q] - '0') <= 9) { v = v * 10 + d; ++q; if (v > 255) return false; }
+    const bool isR = t[q] == 'R';
+    q += isR ? 1 : 0;
+    unsigned d, v = 0;
+    int nd = 0;
+    while ((d = t[q] - '0') <= 9 && v <= 255) { v = v * 10 + d; ++q; ++nd; }
     skip_token();
     r = v;
-    return true;
+    return isR && nd > 0 && v <= 255;
   }
 };
 
@@ -123,29 +127,31 @@ TI_HD int oprnd_type_of(unsigned op, unsigned sp) {
 // `kind` receives bit0 = has addresses (mem_width > 0), bit1 = eligible for the stride path.
 TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P, uint32_t chunk_text_base,
                               ti_inst_rec &r, unsigned &kind) {
+#define TI_FAIL(cond, code) do { if ((cond) && !fl) fl = (code); } while (0)
   Reader rd = {text, q0};
-  uint64_t u;
+  uint32_t fl = 0;  // first error wins, as in the sequential reference
+  uint64_t u = 0;
   kind = 0;
   r.pc = r.mask = r.opc_off = 0; r.mem_idx = 0xFFFFFFFFu;
   r.dst = 0; r.src[0] = r.src[1] = r.src[2] = r.src[3] = 0;
   r.opcode_id = 0; r.op = OP_ALU; r.pack_a = (uint8_t)(SP_OTHER | (0u << 5)); r.pack_b = r.pack_c = 0;
   r.data_size = r.cycles = 0; r.latency = 0; r.initiation_interval = 0; r.opcode_len = 0;
 
-  if (P.trace_version < 3)  // trace_parser.cc:136-143
-    for (int i = 0; i < 4; ++i) { rd.skip_ws(); if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER; }
-  rd.skip_ws(); if (!rd.hex(8, u)) return TI_EF_BAD_NUMBER;
+  if (P.trace_version < 3)  // trace_parser.cc:136-143 (warp-uniform)
+    for (int i = 0; i < 4; ++i) { rd.skip_ws(); TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER); }
+  rd.skip_ws(); TI_FAIL(!rd.hex(8, u), TI_EF_BAD_NUMBER);
   r.pc = (uint32_t)u;
-  rd.skip_ws(); if (!rd.hex(8, u)) return TI_EF_BAD_NUMBER;
+  rd.skip_ws(); TI_FAIL(!rd.hex(8, u), TI_EF_BAD_NUMBER);
   r.mask = (uint32_t)u;
-  rd.skip_ws(); if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
-  if (u > 1) return TI_EF_TOO_MANY_REGS;
-  const unsigned ndst = (unsigned)u;
+  rd.skip_ws(); TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
+  TI_FAIL(u > 1, TI_EF_TOO_MANY_REGS);
+  const unsigned ndst = u ? 1u : 0u;
   unsigned rv = 0;
-  if (ndst) { rd.skip_ws(); if (!rd.reg(rv)) return TI_EF_BAD_REG; r.dst = (uint8_t)rv; }
+  if (ndst) { rd.skip_ws(); TI_FAIL(!rd.reg(rv), TI_EF_BAD_REG); r.dst = (uint8_t)rv; }
 
   // ---- opcode token: mnemonic key, first 16 bytes, width / STRONG / GPU modifiers
   rd.skip_ws();
-  if (rd.peek() == '\n') return TI_EF_TRUNCATED;
+  TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
   const int qo = rd.q;
   uint64_t w0 = 0, w1 = 0, tok8 = 0;
   int len = 0, dot = -1, tlen = 0;
@@ -180,33 +186,34 @@ TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P
     ++len;
   }
   if (dot < 0) dot = len;
-  if (len > 255) return TI_EF_LONG_OPCODE;
+  TI_FAIL(len > 255, TI_EF_LONG_OPCODE);
   r.opc_off = chunk_text_base + (uint32_t)qo;
   r.opcode_len = (uint8_t)len;
 
   rd.skip_ws();
-  if (rd.peek() == '\n') return TI_EF_TRUNCATED;
-  if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
-  if (u > 4) return TI_EF_TOO_MANY_REGS;
-  const unsigned nsrc = (unsigned)u;
-  for (unsigned i = 0; i < nsrc; ++i) { rd.skip_ws(); if (!rd.reg(rv)) return TI_EF_BAD_REG; r.src[i] = (uint8_t)rv; }
+  TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
+  TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
+  TI_FAIL(u > 4, TI_EF_TOO_MANY_REGS);
+  const unsigned nsrc = u > 4 ? 4u : (unsigned)u;
+  for (unsigned i = 0; i < nsrc; ++i) { rd.skip_ws(); TI_FAIL(!rd.reg(rv), TI_EF_BAD_REG); r.src[i] = (uint8_t)rv; }
   rd.skip_ws();
-  if (rd.peek() == '\n') return TI_EF_TRUNCATED;
-  if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
-  const bool has_mem = u != 0;
+  TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
+  TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
+  const bool has_mem = !fl && u != 0;
   unsigned mode = 0;
   if (has_mem) {
-    if (wbad) return TI_EF_BAD_NUMBER;
-    if (width > 255) return TI_EF_BAD_WIDTH;
+    TI_FAIL(wbad, TI_EF_BAD_NUMBER);
+    TI_FAIL(width > 255, TI_EF_BAD_WIDTH);
     rd.skip_ws();
-    if (rd.peek() == '\n') return TI_EF_TRUNCATED;
-    if (!rd.dec(0xffffffffull, u)) return TI_EF_BAD_NUMBER;
+    TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
+    TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
     mode = u > 3 ? 3u : (unsigned)u;
     kind = 1;
   }
 
   // ---- mnemonic -> (opcode id, op_type), trace_driven.cc:188-206
-  if (dot == 0 || dot > TI_ISA_MAX_NAME) return TI_EF_UNKNOWN_OPCODE;
+  const bool keyable = dot > 0 && dot <= TI_ISA_MAX_NAME;
+  if (!keyable) dot = 1;  // keep the shifts below defined; the lookup result is discarded
   const uint64_t klo = dot >= 8 ? w0 : (w0 & ((1ull << (8 * dot)) - 1));
   const uint32_t khi = dot <= 8 ? 0u : (uint32_t)(w1 & ((1ull << (8 * (dot - 8))) - 1));
   unsigned id = 0, cat = 0;
@@ -216,7 +223,7 @@ TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P
     if (!sid) break;
     if (s.x == (uint32_t)klo && s.y == (uint32_t)(klo >> 32) && s.z == khi) { id = sid; cat = (s.w >> 8) & 0xff; break; }
   }
-  if (!id) return TI_EF_UNKNOWN_OPCODE;
+  TI_FAIL(!id || !keyable, TI_EF_UNKNOWN_OPCODE);
   unsigned op = cat, sp = __ldg(P.spop + id);
   const int ot = oprnd_type_of(op, sp);  // before the overrides below (trace_driven.cc:201)
   if (id == TI_OP_MUFU && w1 == 0 && len == 8) {  // whole-string compares, trace_driven.cc:208-217
@@ -253,10 +260,10 @@ TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P
     case TI_OP_HSET2: case TI_OP_HSETP2: init /= 2; break;
     default: break;
   }
-  if (need_w && data_size == 0) return TI_EF_ZERO_WIDTH;
+  TI_FAIL(need_w && data_size == 0, TI_EF_ZERO_WIDTH);
   // a ld/st-class opcode without addresses trips the reference's assert at
   // abstract_hardware_model.cc:296 as soon as one lane is active
-  if (!has_mem && r.mask && (op == OP_LOAD || op == OP_STORE || op == OP_TLOAD || op == OP_TSTORE)) return TI_EF_UNDEF_SPACE;
+  TI_FAIL(!has_mem && r.mask && (op == OP_LOAD || op == OP_STORE || op == OP_TLOAD || op == OP_TSTORE), TI_EF_UNDEF_SPACE);
   r.opcode_id = (uint8_t)id; r.op = (uint8_t)op;
   r.pack_a = (uint8_t)(sp | (unsigned)(ot + 1) << 5);
   r.pack_b = (uint8_t)(nsrc | ndst << 3 | memory_op << 4 | (atomic ? 1u : 0u) << 6 | (cconst ? 1u : 0u) << 7);
@@ -266,7 +273,9 @@ TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P
   if (has_mem) r.mem_idx = memtmp_make((unsigned)rd.q, mode, resolve);
   // base+stride global loads/stores take the thread-per-instruction path (ti_mem.cuh)
   if (has_mem && mode == 1 && space == SPACE_GLOBAL && !atomic && (op == OP_LOAD || op == OP_STORE)) kind |= 2;
-  return 0;
+  if (fl) kind = 0;
+  return fl;
+#undef TI_FAIL
 }
 
 }  // namespace ti

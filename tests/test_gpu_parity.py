@@ -66,12 +66,12 @@ def test_staging_overflow_and_capacity_retry(cuda_parser, tmp_path):
     transactions per chunk than the smem staging area and than the default output
     capacity -- exercises the recompute path and the exact-size re-decode."""
     lines = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (16 * i, 0x7F0000000000 + 4096 * i) for i in range(400)]
-    img = edge_cases.image([(b, 0, 0, [lines] * 4) for b in range(8)])
+    img = edge_cases.image([(b, 0, 0, [lines] * 2) for b in range(16)])  # block dim 64: two warps per block
     path = os.path.join(str(tmp_path), "k.traceg")
     open(path, "wb").write(img)
     k = cuda_parser.parse_kernel_info(path)
     d = k.run()
-    assert len(d.txn) == 32 * len(d.inst) == 32 * 400 * 4 * 8
+    assert len(d.txn) == 32 * len(d.inst) == 32 * 400 * 2 * 16
     o = T.load_dump(harness.oracle_dump(path, str(tmp_path)))
     parity_cases.check_against_dump(d, o, offsets=harness.oracle_kind() == "port")
     cuda_parser.kernel_finalizer(k)
