@@ -42,6 +42,9 @@ namespace ti {
 #ifndef TI_TXN_STAGE
 #define TI_TXN_STAGE 1024
 #endif
+#ifndef TI_MIN_BLOCKS
+#define TI_MIN_BLOCKS 2   // resident CTAs per SM the register allocation is bounded for
+#endif
 constexpr int kChunk = TI_CHUNK;        // bytes of text owned by one chunk
 constexpr int kThreads = TI_THREADS;    // threads per CTA
 constexpr int kWarps = kThreads / 32;
@@ -77,16 +80,17 @@ TI_HD uint32_t isa_hash(uint64_t lo, uint32_t hi) {
   return (uint32_t)(x >> 17) & (kIsaSlots - 1);
 }
 
-// -------------------------------------------------------- look-back descriptor
-// One per chunk and per scan, zeroed before launch.  flag: 0 = nothing yet,
-// 1 = this chunk's aggregate published, 2 = inclusive prefix published.
-template <int NV> struct LookBack {
-  uint32_t flag;
-  uint32_t agg[NV];
-  uint64_t incl[NV];
-};
-typedef LookBack<4> State1;   // inst, mem, tb, warp-header counts
-typedef LookBack<1> State2;   // transaction count
+// -------------------------------------------------------- look-back descriptors
+// One per chunk and per scan, zeroed before launch.  Every 64-bit word carries its own
+// "valid" bit next to the value, so a reader needs no fence: it either sees a complete
+// word or keeps polling (single-copy atomic 8-byte loads/stores).
+//   State1.agg : bit 63 valid | n_warp << 42 | n_tb << 28 | n_mem << 14 | n_inst   (this chunk)
+//   State1.inc0: bit 63 valid | mem << 31 | inst          (inclusive prefix, 31 bits each)
+//   State1.inc1: bit 63 valid | warp << 31 | tb
+//   State2.w   : bit 63 inclusive valid | bit 62 aggregate valid | transaction count
+struct State1 { unsigned long long agg, inc0, inc1, pad; };
+struct State2 { unsigned long long w; };
+constexpr unsigned long long kValid = 1ull << 63, kAggValid = 1ull << 62;
 
 struct Globals {        // zeroed before launch
   uint32_t ticket;      // next chunk to hand out

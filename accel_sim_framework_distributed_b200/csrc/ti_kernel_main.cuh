@@ -17,7 +17,7 @@ TI_D void flush_counters(uint32_t *cnt, unsigned long long *g) {
   }
 }
 
-__global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams P) {
+__global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(const DecodeParams P) {
   TI_DYN_SMEM(smem);
   ti_inst_rec *recs = reinterpret_cast<ti_inst_rec *>(smem + oRecs);
   ti_txn_rec *stage = reinterpret_cast<ti_txn_rec *>(smem + oStage);
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
     if (wid == 0) {
       const uint32_t agg[4] = {n_inst, n_mem, n_tb, n_warp};
       uint64_t ex[4];
-      lookback<4>(P.state1, chunk, agg, ex);
+      lookback1(P.state1, chunk, agg, ex);
       if (lane == 0) { ms->base_inst = ex[0]; ms->base_mem = ex[1]; ms->base_tb = ex[2]; ms->base_warp = ex[3]; }
     }
     __syncthreads();
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
       if (base_mem + n_mem > P.cap_mem) ov |= 2;
       if (base_tb + n_tb > P.cap_tb) ov |= 8;
       if (base_warp + n_warp > P.cap_warp) ov |= 16;
-      if (base_inst + n_inst > 0xfffffffeull || base_mem + n_mem > 0xfffffffeull) ov |= 32;
+      if (base_inst + n_inst > 0x7ffffffeull || base_mem + n_mem > 0x7ffffffeull) ov |= 32;  // 31-bit prefix fields
       if (ov) atomicOr(&P.g->overflow, ov);
     }
 
@@ -289,14 +289,16 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
 #pragma unroll 4
         for (unsigned l = 0; l < 32; l += 2) dst[l >> 1] = make_ulonglong2(stride_addr(d, l), stride_addr(d, l + 1));
       }
-      const unsigned n_txn = (fl || !mask) ? 0u : stride_count(d, ds, seg);
+      const bool dense = !fl && mask && stride_is_dense(d, ds);
+      const unsigned n_txn = (fl || !mask) ? 0u : dense ? dense_count(d, ds, seg) : stride_count(d, ds, seg);
       uint32_t slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
       if (slot + n_txn > (uint32_t)kTxnStage) slot = 0xFFFFu;
       txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
       rp->mem_idx = (uint32_t)row;
       if (n_txn && slot != 0xFFFFu) {
         const unsigned is_write = op == OP_STORE ? 1u : 0u;
-        stride_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
+        if (dense) dense_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
+        else stride_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
       }
     }
     __syncthreads();
@@ -366,10 +368,8 @@ __global__ void __launch_bounds__(kThreads) ti_decode_kernel(const DecodeParams 
         n_mem, ms->warp_tot, [&](uint32_t i) { return (uint32_t)txn_cnt[i]; },
         [&](uint32_t i, uint32_t ex, uint32_t) { txn_loc[i] = (uint16_t)ex; });
     if (wid == 0) {
-      const uint32_t agg[1] = {n_txn_chunk};
-      uint64_t ex[1];
-      lookback<1>(P.state2, chunk, agg, ex);
-      if (lane == 0) ms->base_txn = ex[0];
+      const uint64_t ex = lookback2(P.state2, chunk, n_txn_chunk);
+      if (lane == 0) ms->base_txn = ex;
     }
     __syncthreads();
     const uint64_t base_txn = ms->base_txn;

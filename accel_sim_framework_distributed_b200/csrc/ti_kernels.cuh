@@ -108,55 +108,68 @@ TI_D uint64_t warp_sum_u64(uint64_t v) {
 }
 
 // Chained scan with decoupled look-back (single pass): publishes this chunk's
-// aggregate, sums the aggregates of the predecessors that have not finished yet
-// plus the nearest published inclusive prefix, then publishes its own inclusive
-// prefix.  Chunks are handed out in order by the ticket, so every predecessor is
-// already running.  Executed by one full warp.
-template <int NV>
-TI_D void lookback(LookBack<NV> *st, uint32_t c, const uint32_t (&agg)[NV], uint64_t (&excl)[NV]) {
+// aggregate, sums the aggregates of the predecessors that have not finished yet plus
+// the nearest published inclusive prefix, then publishes its own inclusive prefix.
+// Chunks are handed out in order by the ticket, so every predecessor is already
+// running.  Executed by one full warp; lane k inspects chunk c-1-k.
+TI_D unsigned long long ld_vol64(const unsigned long long *p) { return *reinterpret_cast<const volatile unsigned long long *>(p); }
+TI_D void st_vol64(unsigned long long *p, unsigned long long v) { *reinterpret_cast<volatile unsigned long long *>(p) = v; }
+
+TI_D void lookback1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64_t (&excl)[4]) {
   const unsigned lane = lane_id();
-#pragma unroll
-  for (int k = 0; k < NV; ++k) excl[k] = 0;
-  if (c == 0) {
-    if (lane == 0) {
-      for (int k = 0; k < NV; ++k) { st[0].agg[k] = agg[k]; st[0].incl[k] = agg[k]; }
-      __threadfence();
-      atomicExch(&st[0].flag, 2u);
-    }
-    __syncwarp();
-    return;
-  }
-  if (lane == 0) {
-    for (int k = 0; k < NV; ++k) st[c].agg[k] = agg[k];
-    __threadfence();
-    atomicExch(&st[c].flag, 1u);
-  }
-  for (int64_t idx = (int64_t)c - 1;; idx -= 32) {
+  if (lane == 0)
+    st_vol64(&st[c].agg, kValid | (unsigned long long)agg[3] << 42 | (unsigned long long)agg[2] << 28 |
+                             (unsigned long long)agg[1] << 14 | agg[0]);
+  excl[0] = excl[1] = excl[2] = excl[3] = 0;
+  for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= 32) {
     const int64_t j = idx - lane;
-    uint32_t f;
+    unsigned long long A = kValid, I0 = kValid, I1 = kValid;  // chunks before the first: inclusive prefix 0
     for (;;) {
-      f = j >= 0 ? ld_flag(&st[j].flag) : 2u;
-      if (!__any_sync(kFull, f == 0)) break;
-      __nanosleep(40);
+      if (j >= 0) { I0 = ld_vol64(&st[j].inc0); I1 = ld_vol64(&st[j].inc1); A = ld_vol64(&st[j].agg); }
+      const bool ready = ((I0 & I1) | A) >> 63;
+      if (__all_sync(kFull, ready)) break;
+      __nanosleep(64);
     }
-    __threadfence();
-    const uint32_t have = __ballot_sync(kFull, f == 2);
+    const bool hasinc = (I0 & I1) >> 63;
+    const uint32_t have = __ballot_sync(kFull, hasinc);
     const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      uint64_t v = 0;
-      if (j >= 0 && lane < L) v = ld_vol(&st[j].agg[k]);
-      else if (j >= 0 && lane == L) v = ld_vol(&st[j].incl[k]);
-      excl[k] += warp_sum_u64(v);
+    const bool useagg = lane < L;                      // A is valid for these lanes
+    excl[0] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A & 0x3fff) : 0u);
+    excl[1] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 14 & 0x3fff) : 0u);
+    excl[2] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 28 & 0x3fff) : 0u);
+    excl[3] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 42 & 0x3fff) : 0u);
+    if (L < 32) {
+      const unsigned long long i0 = __shfl_sync(kFull, I0, L), i1 = __shfl_sync(kFull, I1, L);
+      excl[0] += i0 & 0x7fffffffull; excl[1] += i0 >> 31 & 0x7fffffffull;
+      excl[2] += i1 & 0x7fffffffull; excl[3] += i1 >> 31 & 0x7fffffffull;
+      break;
     }
-    if (L < 32) break;
   }
   if (lane == 0) {
-    for (int k = 0; k < NV; ++k) st[c].incl[k] = excl[k] + agg[k];
-    __threadfence();
-    atomicExch(&st[c].flag, 2u);
+    st_vol64(&st[c].inc0, kValid | (excl[1] + agg[1]) << 31 | (excl[0] + agg[0]));
+    st_vol64(&st[c].inc1, kValid | (excl[3] + agg[3]) << 31 | (excl[2] + agg[2]));
   }
-  __syncwarp();
+}
+
+TI_D uint64_t lookback2(State2 *st, uint32_t c, uint32_t agg) {
+  const unsigned lane = lane_id();
+  if (lane == 0 && c) st_vol64(&st[c].w, kAggValid | agg);
+  uint64_t excl = 0;
+  for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= 32) {
+    const int64_t j = idx - lane;
+    unsigned long long W = kValid;
+    for (;;) {
+      if (j >= 0) W = ld_vol64(&st[j].w);
+      if (__all_sync(kFull, (W >> 62) != 0)) break;
+      __nanosleep(64);
+    }
+    const uint32_t have = __ballot_sync(kFull, (W >> 63) != 0);
+    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
+    excl += __reduce_add_sync(kFull, lane < L ? (uint32_t)(W & 0xffffffffull) : 0u);
+    if (L < 32) { excl += __shfl_sync(kFull, W, L) & 0x3fffffffffffffffull; break; }
+  }
+  if (lane == 0) st_vol64(&st[c].w, kValid | (excl + agg));
+  return excl;
 }
 
 TI_D void note_error(Misc *ms, uint32_t flags, uint32_t off) {

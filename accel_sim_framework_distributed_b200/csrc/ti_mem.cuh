@@ -195,6 +195,44 @@ TI_D unsigned stride_count(const StrideDesc &d, unsigned ds, unsigned seg) {
   return cnt;
 }
 
+// ---- dense progression: stride == data size and an aligned base.  The run then covers
+// one contiguous byte range with no access crossing a segment, so every transaction
+// follows in closed form from its block: O(transactions), not O(lanes).  This is the
+// shape of every unit-stride access of a real trace (and all of BASELINE config 2).
+TI_D bool stride_is_dense(const StrideDesc &d, unsigned ds) {
+  return d.n > 0 && d.stride == (int64_t)ds && d.base != 0 && (d.base & (ds - 1)) == 0;
+}
+TI_D unsigned dense_count(const StrideDesc &d, unsigned ds, unsigned seg) {
+  const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)d.n * ds;
+  return (unsigned)((((end - 1) & segmask) - (d.base & segmask)) / seg) + 1;
+}
+TI_D unsigned dense_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out) {
+  const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)d.n * ds;
+  const unsigned sh = ds == 1 ? 0 : ds == 2 ? 1 : ds == 4 ? 2 : ds == 8 ? 3 : 4;
+  unsigned n = 0;
+  for (uint64_t S = d.base & segmask; S < end; S += seg, ++n) {
+    const uint64_t lo = S > d.base ? S : d.base, hi = S + seg < end ? S + seg : end;
+    const unsigned i0 = (unsigned)((lo - d.base) >> sh), i1 = (unsigned)((hi - d.base) >> sh);  // lanes [i0, i1) of the run
+    const unsigned p0 = (unsigned)(lo & 127), p1 = p0 + (unsigned)(hi - lo);                 // bytes [p0, p1) of the 128 B line
+    Txn x;
+    x.block = S;
+    x.lanes = (i1 - i0 == 32 ? 0xffffffffu : ((1u << (i1 - i0)) - 1)) << (d.first + i0);
+    x.chunks = 0;
+#pragma unroll
+    for (unsigned w = 0; w < 4; ++w) {
+      const unsigned a = p0 > 32 * w ? p0 : 32 * w, b = p1 < 32 * w + 32 ? p1 : 32 * w + 32;
+      const bool hit = b > a;
+      x.bytes[w] = hit ? ((b - a == 32 ? 0xffffffffu : ((1u << (b - a)) - 1)) << (a - 32 * w)) : 0u;
+      x.chunks |= hit ? 1u << w : 0u;
+    }
+    const ti_txn_rec r = reduce_and_send(x, seg, type, is_write);
+    const uint4 *src = reinterpret_cast<const uint4 *>(&r);
+    uint4 *dst = reinterpret_cast<uint4 *>(out + n);
+    dst[0] = src[0]; dst[1] = src[1];
+  }
+  return n;
+}
+
 struct OpenTxn { uint32_t lanes, b0, b1, b2, b3, chunks; };
 TI_D void open_clear(OpenTxn &t) { t.lanes = t.b0 = t.b1 = t.b2 = t.b3 = t.chunks = 0; }
 TI_D void open_touch(OpenTxn &t, uint64_t a, unsigned ds, unsigned lane) {

@@ -226,20 +226,21 @@ def bench_b200(args):
 
     # ---- end-to-end arm: host buffers through the C ABI, copies inside the timed region
     ke = tp.open_buffer(body, hdr)
-    import ctypes
-    pin = torch.from_numpy(body)
-    torch.cuda.cudart().cudaHostRegister(pin.data_ptr(), pin.numel(), 0)
-    for _ in range(max(1, min(args.warmup, 2))):
-        ke.upload(); ke.decode(); ke.sync(); view = ke.fetch()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 3))
-    for _ in range(e2e_steps):
-        ke.upload(); ke.decode(); ke.sync(); view = ke.fetch()
-    torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
-    d2h = 32 * len(view.inst) + 256 * len(view.rows) + 4 * len(view.txn_off) + 32 * len(view.txn) + 32 * len(view.tb) + 16 * len(view.warp)
-    torch.cuda.cudart().cudaHostUnregister(pin.data_ptr())
+    e2e_s, d2h = float("nan"), 0
+    if not args.no_e2e:
+        pin = torch.from_numpy(body)
+        torch.cuda.cudart().cudaHostRegister(pin.data_ptr(), pin.numel(), 0)
+        for _ in range(max(1, min(args.warmup, 2))):
+            ke.upload(); ke.decode(); ke.sync(); view = ke.fetch()
+        barrier()
+        t0 = time.perf_counter()
+        e2e_steps = max(1, min(args.steps, 3))
+        for _ in range(e2e_steps):
+            ke.upload(); ke.decode(); ke.sync(); view = ke.fetch()
+        torch.cuda.synchronize()
+        e2e_s = (time.perf_counter() - t0) / e2e_steps
+        d2h = 32 * len(view.inst) + 256 * len(view.rows) + 4 * len(view.txn_off) + 32 * len(view.txn) + 32 * len(view.tb) + 16 * len(view.warp)
+        torch.cuda.cudart().cudaHostUnregister(pin.data_ptr())
 
     # ---- max over ranks
     stats = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device="cuda")
@@ -298,6 +299,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="tuning sweeps only: skip the host-buffer arm")
     args = ap.parse_args()
     if args.impl == "reference":
         bench_reference(args)
