@@ -387,18 +387,22 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
     for (uint32_t mo = tid; mo < n_mem; mo += kThreads)
       if (base_mem + mo < P.cap_mem) P.txn_off[base_mem + mo] = (uint32_t)(base_txn + txn_loc[mo]);
-    // staged transactions: 16 B per thread, two threads per record
-    for (uint32_t mo = wid; mo < n_mem; mo += kWarps) {
+    // staged transactions -> HBM in file order: one thread moves one instruction's records
+    // (32 instructions per warp in flight; a warp per instruction left 3/4 of the lanes idle)
+    for (uint32_t mo = tid; mo < n_mem; mo += kThreads) {
       const uint32_t n = txn_cnt[mo], slot = txn_slot[mo];
+      if (!n || slot == 0xFFFFu) continue;
       const uint64_t at = base_txn + txn_loc[mo];
-      if (!n) continue;
-      if (slot != 0xFFFFu) {
-        const uint4 *src = reinterpret_cast<const uint4 *>(stage + slot);
-        uint4 *dst = reinterpret_cast<uint4 *>(P.txn + at);
-        for (uint32_t k = lane; k < 2 * n; k += 32)
-          if (at + (k >> 1) < P.cap_txn) dst[k] = src[k];
-      } else {
-        // overflowed the staging area: coalesce again from the row written in P6
+      const uint4 *src = reinterpret_cast<const uint4 *>(stage + slot);
+      uint4 *dst = reinterpret_cast<uint4 *>(P.txn + at);
+      for (uint32_t k = 0; k < n; ++k)
+        if (at + k < P.cap_txn) { dst[2 * k] = src[2 * k]; dst[2 * k + 1] = src[2 * k + 1]; }
+    }
+    if (ms->stage_used > (uint32_t)kTxnStage) {      // warp-uniform: some instructions did not fit the staging area
+      for (uint32_t mo = wid; mo < n_mem; mo += kWarps) {
+        if (txn_slot[mo] != 0xFFFFu || !txn_cnt[mo]) continue;
+        // coalesce again from the row written in P6
+        const uint64_t at = base_txn + txn_loc[mo];
         const ti_inst_rec *rp = recs + mem_list[mo];
         const uint64_t row = base_mem + mo;
         const uint64_t addr = row < P.cap_mem ? __ldcg(P.rows + row * 32 + lane) : 0;
