@@ -40,7 +40,7 @@ namespace ti {
 #define TI_THREADS 256
 #endif
 #ifndef TI_TXN_STAGE
-#define TI_TXN_STAGE 1024
+#define TI_TXN_STAGE 768
 #endif
 #ifndef TI_MIN_BLOCKS
 #define TI_MIN_BLOCKS 2   // resident CTAs per SM the register allocation is bounded for

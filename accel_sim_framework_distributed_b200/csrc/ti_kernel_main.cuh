@@ -33,6 +33,8 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
   uint32_t *cnt = reinterpret_cast<uint32_t *>(smem + oCnt);
   uint16_t *nlmap = reinterpret_cast<uint16_t *>(smem + oNlMap);
   const uint32_t *nlmap32 = reinterpret_cast<const uint32_t *>(smem + oNlMap);
+  uint16_t *dlmap = reinterpret_cast<uint16_t *>(smem + oDlMap);
+  const uint32_t *dlmap32 = reinterpret_cast<const uint32_t *>(smem + oDlMap);
   uint32_t *wscratch = reinterpret_cast<uint32_t *>(smem + oTok + (threadIdx.x >> 5) * kWarpScratch);
   uint16_t *tokpos = reinterpret_cast<uint16_t *>(wscratch);
   Misc *ms = reinterpret_cast<Misc *>(smem + oMisc);
@@ -118,7 +120,11 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     // Counts are packed 2 x 16 bit: instruction lines | structural lines.
     const uint32_t lim = (uint32_t)(P.len - cb < (uint64_t)kChunk ? P.len - cb : (uint64_t)kChunk);
     for (int v = tid; v < kTextBytes / 16; v += kThreads)
-      if (v == 0 || v > kChunk / 16) nlmap[v] = (uint16_t)nl_mask16(text_v[v]);
+      if (v == 0 || v > kChunk / 16) {
+        uint32_t nl16, dl16;
+        cls_masks16(text_v[v], nl16, dl16);
+        nlmap[v] = (uint16_t)nl16; dlmap[v] = (uint16_t)dl16;
+      }
     uint32_t starts[kVecIters];
     uint32_t excl[kVecIters];
     uint32_t run = 0;
@@ -126,8 +132,11 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     for (int it = 0; it < kVecIters; ++it) {
       const uint32_t v = wid * kVecPerWarp + it * 32 + lane, s0 = v * 16;
       const bool inside = v < (uint32_t)(kChunk / 16);
-      const uint32_t m = inside ? nl_mask16(text_v[1 + v]) : 0u;
-      if (inside) nlmap[1 + v] = (uint16_t)m;
+      uint32_t m = 0, dl16 = 0;
+      if (inside) {
+        cls_masks16(text_v[1 + v], m, dl16);
+        nlmap[1 + v] = (uint16_t)m; dlmap[1 + v] = (uint16_t)dl16;
+      }
       const uint32_t up = __shfl_up_sync(kFull, m, 1);
       const uint32_t prev = lane ? (up >> 15) & 1 : (inside && text[16 + s0 - 1] == '\n');
       uint32_t st = ((m << 1) | prev) & ~m & 0xffffu;
@@ -178,8 +187,9 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       ti_inst_rec r;
       unsigned kd;
       const unsigned o = inst_off[io];
-      uint32_t fl = parse_inst_line(text, (int)o, P, tbase, r, kd);
-      if (line_end(nlmap32, o) - o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
+      const unsigned le = line_end(nlmap32, o);
+      uint32_t fl = parse_inst_line(text, dlmap32, (int)o, le, P, tbase, r, kd);
+      if (le - o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
       if (fl) { note_error(ms, fl, tbase + o); kd = 0; r.mem_idx = 0xFFFFFFFFu; r.pack_c &= 0x7f; }
       const uint4 *src = reinterpret_cast<const uint4 *>(&r);
       uint4 *dst = reinterpret_cast<uint4 *>(recs + io);

@@ -56,7 +56,8 @@ constexpr int oCnt = oKind + align16(kRecCap);               // u32[kSmCnt]   co
 constexpr int kWarpScratch = 32 * 6 * 4;                     // per warp: token offsets (decode), then B-group merge slots (coalesce)
 constexpr int oTok = oCnt + align16(kSmCnt * 4);
 constexpr int oNlMap = oTok + kWarps * kWarpScratch;      // u16[kTextBytes/16] newline bitmap of the staged text
-constexpr int oMisc = oNlMap + align16(kTextBytes / 16 * 2 + 4);
+constexpr int oDlMap = oNlMap + align16(kTextBytes / 16 * 2 + 4);  // u16[kTextBytes/16] delimiter bitmap (' ', 0x09..0x0d)
+constexpr int oMisc = oDlMap + align16(kTextBytes / 16 * 2 + 4);
 constexpr int kSmemBytes = oMisc + align16((int)sizeof(Misc));
 static_assert(kTextBytes % 16 == 0 && kChunk % 16 == 0 && kThreads % 32 == 0, "chunk geometry");
 static_assert(kTextBytes < 65536, "smem offsets are 16 bit");

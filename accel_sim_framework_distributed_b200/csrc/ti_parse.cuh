@@ -14,6 +14,7 @@
 #define TI_PARSE_CUH
 
 #include "ti_device.cuh"
+#include "ti_lex.cuh"
 
 #define TI_OPCODE_IDS_ONLY
 #define TI_ISA_BEGIN
@@ -85,8 +86,8 @@ struct Reader {
     return ok;
   }
   // hexadecimal with optional 0x, at most `maxd` significant digits
-  TI_D bool hex(int maxd, uint64_t &v) {
-    if (t[q] == '0' && (t[q + 1] | 0x20) == 'x' && !is_end(t[q + 2])) q += 2;
+  TI_D bool hex(int maxd, uint64_t &v, bool prefix = true) {
+    if (prefix && t[q] == '0' && (t[q + 1] | 0x20) == 'x' && !is_end(t[q + 2])) q += 2;
     uint64_t m = 0;
     int nsig = 0, ntot = 0;
     unsigned d;
@@ -123,14 +124,110 @@ TI_HD int oprnd_type_of(unsigned op, unsigned sp) {
   return -1;
 }
 
-// Decodes the instruction line starting at smem offset q0.  Returns TI_EF_* flags.
+// ---- token decoders over (offset, length); the fast shapes use SWAR, anything else the
+// character loops of Reader (same semantics, see the header comment of ti_lex.cuh)
+TI_D bool tok_hex(const Lex &lx, unsigned b, unsigned n, int maxd, uint64_t &v) {
+  if (n > 2 && lx.t[b] == '0' && (lx.t[b + 1] | 0x20) == 'x') { b += 2; n -= 2; }
+  if (n > (unsigned)maxd) {              // leading zeros or too many digits: exact loop
+    Reader rd = {lx.t, (int)b};
+    const bool ok = rd.hex(maxd, v, false);
+    return ok && rd.q == (int)(b + n);
+  }
+  uint32_t hv;
+  bool ok = true;
+  v = 0;
+  unsigned k = n & 3;                    // leading partial group, then groups of four
+  if (k) { ok = hex4(load4(lx.t32, b), k, hv); v = hv; }
+  for (; k < n; k += 4) { ok = hex4(load4(lx.t32, b + k), 4, hv) && ok; v = v << 16 | hv; }
+  return ok;
+}
+TI_D bool tok_dec(const Lex &lx, unsigned b, unsigned n, uint64_t max, uint64_t &v) {
+  if (n > 8) {                           // long decimals: exact loop
+    Reader rd = {lx.t, (int)b};
+    const bool ok = rd.dec(max, v);
+    return ok && rd.q == (int)(b + n);
+  }
+  uint64_t x = load8(lx.t32, b);
+  uint32_t m = 0;
+  bool ok = n > 0;
+  for (unsigned k = 0; k < n; ++k, x >>= 8) { const unsigned d = (unsigned)(x & 0xff) - '0'; ok = ok && d <= 9; m = m * 10 + d; }
+  v = m;
+  return ok && m <= max;
+}
+TI_D bool tok_reg(const Lex &lx, unsigned b, unsigned n, unsigned &r) {  // "R<digits>[suffix]", 0..255
+  uint64_t x = load8(lx.t32, b);
+  const bool isR = (x & 0xff) == 'R';
+  x >>= 8;
+  unsigned v = 0, nd = 0;
+  const unsigned lim = n - 1 < 7 ? n - 1 : 7;
+  unsigned d;
+  while (nd < lim && (d = (unsigned)(x & 0xff) - '0') <= 9 && v <= 255) { v = v * 10 + d; ++nd; x >>= 8; }
+  if (nd == 7) {                         // more than seven digits: exact loop
+    Reader rd = {lx.t, (int)b};
+    return rd.reg(r);
+  }
+  r = v;
+  return isR && nd > 0 && v <= 255;
+}
+
+// 0x80 in every byte of a 64-bit word that equals '.'
+TI_HD uint64_t dots64(uint64_t w) {
+  const uint64_t y = w ^ 0x2e2e2e2e2e2e2e2eull;
+  return ~(((y & 0x7f7f7f7f7f7f7f7full) + 0x7f7f7f7f7f7f7f7full) | y | 0x7f7f7f7f7f7f7f7full);
+}
+TI_HD uint64_t keep_bytes(uint64_t w, int n) { return n >= 8 ? w : n <= 0 ? 0ull : (w & ((1ull << (8 * n)) - 1)); }
+
+// Modifier scan of a memory instruction's opcode (trace_parser.cc:62-76 for the width,
+// trace_driven.cc:272-275 for STRONG + GPU).  Dots are located with a SWAR compare per
+// 8-byte window; every dot-separated token of up to 8 characters is tested as a word.
+TI_D void opcode_modifiers(const Lex &lx, unsigned b, unsigned n, uint32_t &width, bool &wbad, bool &strong, bool &gpu) {
+  width = 4; wbad = strong = gpu = false;
+  bool wfound = false;
+  unsigned ts = 0;                                      // start of the current token
+  for (unsigned w0 = 0; w0 < n; w0 += 8) {
+    const uint64_t win = load8(lx.t32, b + w0);
+    uint64_t dm = dots64(keep_bytes(win, (int)(n - w0)));
+    const bool last_window = w0 + 8 >= n;
+    for (;;) {                                          // every token that ends inside this window
+      unsigned te;
+      if (dm) { te = w0 + ((__ffsll((long long)dm) - 1) >> 3); dm &= dm - 1; }
+      else if (last_window) te = n;
+      else break;
+      const unsigned tl = te - ts;
+      if (tl > 0 && tl <= 8) {
+        const uint64_t tok = keep_bytes(load8(lx.t32, b + ts), (int)tl);
+        if (tl == 6 && tok == pack8("STRONG")) strong = true;
+        if (tl == 3 && tok == pack8("GPU")) gpu = true;
+        if (!wfound) {
+          const unsigned skip = (tok & 0xff) == 'U' ? 1u : 0u;   // "U<digits>" counts like "<digits>"
+          uint64_t x = tok >> (8 * skip);
+          uint32_t val = 0;
+          bool dig = tl > skip;
+          for (unsigned k = skip; k < tl; ++k, x >>= 8) { const unsigned d = (unsigned)(x & 0xff) - '0'; dig = dig && d <= 9; val = val * 10 + d; }
+          if (dig) { wfound = true; width = val / 8; }
+        }
+      } else if (tl > 8 && !wfound) {                   // a long token is a width only if all digits: exact loop
+        const unsigned skip = lx.t[b + ts] == 'U' ? 1u : 0u;
+        bool dig = true;
+        uint32_t val = 0;
+        for (unsigned k = skip; k < tl; ++k) { const unsigned d = lx.t[b + ts + k] - '0'; dig = dig && d <= 9; if (k - skip < 10) val = val * 10 + d; }
+        if (dig) { wfound = true; wbad = tl - skip > 9; width = val / 8; }
+      }
+      ts = te + 1;
+      if (te >= n) break;
+    }
+  }
+}
+
+// Decodes the instruction line at smem offsets [q0, le).  Returns TI_EF_* flags.
 // `kind` receives bit0 = has addresses (mem_width > 0), bit1 = eligible for the stride path.
-TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P, uint32_t chunk_text_base,
-                              ti_inst_rec &r, unsigned &kind) {
+TI_D uint32_t parse_inst_line(const uint8_t *text, const uint32_t *dlmap32, int q0, unsigned le, const DecodeParams &P,
+                              uint32_t chunk_text_base, ti_inst_rec &r, unsigned &kind) {
 #define TI_FAIL(cond, code) do { if ((cond) && !fl) fl = (code); } while (0)
-  Reader rd = {text, q0};
+  Lex lx = {text, reinterpret_cast<const uint32_t *>(text), dlmap32, (unsigned)q0, le};
   uint32_t fl = 0;  // first error wins, as in the sequential reference
   uint64_t u = 0;
+  unsigned b, n;
   kind = 0;
   r.pc = r.mask = r.opc_off = 0; r.mem_idx = 0xFFFFFFFFu;
   r.dst = 0; r.src[0] = r.src[1] = r.src[2] = r.src[3] = 0;
@@ -138,78 +235,62 @@ TI_D uint32_t parse_inst_line(const uint8_t *text, int q0, const DecodeParams &P
   r.data_size = r.cycles = 0; r.latency = 0; r.initiation_interval = 0; r.opcode_len = 0;
 
   if (P.trace_version < 3)  // trace_parser.cc:136-143 (warp-uniform)
-    for (int i = 0; i < 4; ++i) { rd.skip_ws(); TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER); }
-  rd.skip_ws(); TI_FAIL(!rd.hex(8, u), TI_EF_BAD_NUMBER);
+    for (int i = 0; i < 4; ++i) { const bool have = lx.next(b, n); TI_FAIL(!have || !tok_dec(lx, b, n, 0xffffffffull, u), TI_EF_BAD_NUMBER); }
+  bool have = lx.next(b, n);
+  TI_FAIL(!have || !tok_hex(lx, b, n, 8, u), TI_EF_BAD_NUMBER);
   r.pc = (uint32_t)u;
-  rd.skip_ws(); TI_FAIL(!rd.hex(8, u), TI_EF_BAD_NUMBER);
+  have = lx.next(b, n);
+  TI_FAIL(!have || !tok_hex(lx, b, n, 8, u), TI_EF_BAD_NUMBER);
   r.mask = (uint32_t)u;
-  rd.skip_ws(); TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
+  have = lx.next(b, n);
+  TI_FAIL(!have || !tok_dec(lx, b, n, 0xffffffffull, u), TI_EF_BAD_NUMBER);
   TI_FAIL(u > 1, TI_EF_TOO_MANY_REGS);
   const unsigned ndst = u ? 1u : 0u;
   unsigned rv = 0;
-  if (ndst) { rd.skip_ws(); TI_FAIL(!rd.reg(rv), TI_EF_BAD_REG); r.dst = (uint8_t)rv; }
+  if (ndst) { have = lx.next(b, n); TI_FAIL(!have || !tok_reg(lx, b, n, rv), TI_EF_BAD_REG); r.dst = (uint8_t)rv; }
 
-  // ---- opcode token: mnemonic key, first 16 bytes, width / STRONG / GPU modifiers
-  rd.skip_ws();
-  TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
-  const int qo = rd.q;
-  uint64_t w0 = 0, w1 = 0, tok8 = 0;
-  int len = 0, dot = -1, tlen = 0;
-  bool alldig = true, restdig = true, firstU = false, wfound = false, wbad = false, strong = false, gpu = false;
-  uint32_t tval = 0, width = 4;
-  int tdig = 0;
-  for (;; ++rd.q) {
-    const unsigned c = rd.peek();
-    const bool end = is_end(c);
-    if (end || c == '.') {
-      if (tlen > 0) {  // token boundary (empty tokens are dropped, trace_parser.cc:56-58)
-        if (!wfound) {
-          const bool num = alldig, unum = firstU && tlen > 1 && restdig;
-          if (num || unum) { wfound = true; wbad = tdig > 9; width = tval / 8; }
-        }
-        if (tlen == 6 && tok8 == pack8("STRONG")) strong = true;
-        if (tlen == 3 && tok8 == pack8("GPU")) gpu = true;
-      }
-      if (end) break;
-      if (dot < 0) dot = len;
-      tlen = 0; tok8 = 0; alldig = restdig = true; firstU = false; tval = 0; tdig = 0;
-    } else {
-      const unsigned d = c - '0';
-      if (tlen == 0) { firstU = c == 'U'; alldig = d <= 9; }
-      else { alldig = alldig && d <= 9; restdig = restdig && d <= 9; }
-      if (d <= 9) { if (tdig < 10) tval = tval * 10 + d; ++tdig; }
-      if (tlen < 8) tok8 |= (uint64_t)c << (8 * tlen);
-      ++tlen;
-    }
-    if (len < 8) w0 |= (uint64_t)c << (8 * len);
-    else if (len < 16) w1 |= (uint64_t)c << (8 * (len - 8));
-    ++len;
+  // ---- opcode token: first 16 bytes, first dot, mnemonic key
+  have = lx.next(b, n);
+  TI_FAIL(!have, TI_EF_TRUNCATED);
+  const unsigned ob = b;
+  const int len = (int)n;
+  const uint64_t w0 = keep_bytes(load8(lx.t32, ob), len), w1 = keep_bytes(load8(lx.t32, ob + 8), len - 8);
+  int dot = len;
+  {
+    const uint64_t d0 = dots64(w0), d1 = dots64(w1);
+    if (d0) dot = (__ffsll((long long)d0) - 1) >> 3;
+    else if (d1) dot = 8 + ((__ffsll((long long)d1) - 1) >> 3);
+    else if (len > 16) dot = 16;                       // a mnemonic this long is in no table
   }
-  if (dot < 0) dot = len;
   TI_FAIL(len > 255, TI_EF_LONG_OPCODE);
-  r.opc_off = chunk_text_base + (uint32_t)qo;
+  r.opc_off = chunk_text_base + ob;
   r.opcode_len = (uint8_t)len;
 
-  rd.skip_ws();
-  TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
-  TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
+  have = lx.next(b, n);
+  TI_FAIL(!have, TI_EF_TRUNCATED);
+  TI_FAIL(!tok_dec(lx, b, n, 0xffffffffull, u), TI_EF_BAD_NUMBER);
   TI_FAIL(u > 4, TI_EF_TOO_MANY_REGS);
   const unsigned nsrc = u > 4 ? 4u : (unsigned)u;
-  for (unsigned i = 0; i < nsrc; ++i) { rd.skip_ws(); TI_FAIL(!rd.reg(rv), TI_EF_BAD_REG); r.src[i] = (uint8_t)rv; }
-  rd.skip_ws();
-  TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
-  TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
+  for (unsigned i = 0; i < nsrc; ++i) { have = lx.next(b, n); TI_FAIL(!have || !tok_reg(lx, b, n, rv), TI_EF_BAD_REG); r.src[i] = (uint8_t)rv; }
+  have = lx.next(b, n);
+  TI_FAIL(!have, TI_EF_TRUNCATED);
+  TI_FAIL(!tok_dec(lx, b, n, 0xffffffffull, u), TI_EF_BAD_NUMBER);
   const bool has_mem = !fl && u != 0;
   unsigned mode = 0;
+  uint32_t width = 4;
+  bool strong = false, gpu = false;
   if (has_mem) {
+    bool wbad;
+    opcode_modifiers(lx, ob, (unsigned)len, width, wbad, strong, gpu);
     TI_FAIL(wbad, TI_EF_BAD_NUMBER);
     TI_FAIL(width > 255, TI_EF_BAD_WIDTH);
-    rd.skip_ws();
-    TI_FAIL(rd.peek() == '\n', TI_EF_TRUNCATED);
-    TI_FAIL(!rd.dec(0xffffffffull, u), TI_EF_BAD_NUMBER);
+    have = lx.next(b, n);
+    TI_FAIL(!have, TI_EF_TRUNCATED);
+    TI_FAIL(!tok_dec(lx, b, n, 0xffffffffull, u), TI_EF_BAD_NUMBER);
     mode = u > 3 ? 3u : (unsigned)u;
     kind = 1;
   }
+  struct { int q; } rd = {(int)lx.q};                 // offset of the first address token's delimiter
 
   // ---- mnemonic -> (opcode id, op_type), trace_driven.cc:188-206
   const bool keyable = dot > 0 && dot <= TI_ISA_MAX_NAME;

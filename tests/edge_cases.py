@@ -116,6 +116,12 @@ W0 = [
     "0320 00000000 0 STG.E.SYS 2 R4 R6 4 1 0x0 0 0",
     # unknown address mode keeps zero addresses (value-initialised inst_memadd_info_t)
     "0330 ffffffff 1 R2 LDG.E.SYS 1 R4 4 3 0x7f000000a000 4 0",
+    # leading zeros beyond the field width, zero-padded counts and register numbers
+    "0000000350 00000000ffffffff 01 R007 FADD 02 R004 R5 00 0",
+    "0000000000000360 ffffffff 1 R2 LDG.E.64.SYS 1 R4 8 1 0x00000000007f000000b000 8 0",
+    # a width token after several modifiers; U-prefixed width; digits-only long token
+    "0370 ffffffff 1 R2 LDG.E.CONSTANT.EF.128.SYS 1 R4 16 1 0x7f000000c000 16 0",
+    "0380 ffffffff 1 R2 LDG.E.LTC128B.U16.CONSTANT 1 R4 2 1 0x7f000000d000 2 0",
     "0340 ffffffff 0 EXIT 0 0 0",
 ]
 
