@@ -57,6 +57,21 @@ class DevView(C.Structure):
     ]
 
 
+class NoAllocIO(C.Structure):
+    """ti_noalloc_io: caller-owned device buffers for ti_decode_noalloc."""
+    _fields_ = [
+        ("d_text", C.c_void_p), ("len", C.c_uint64), ("binary_version", C.c_uint32), ("trace_version", C.c_uint32),
+        ("shmem_base_addr", C.c_uint64), ("local_base_addr", C.c_uint64),
+        ("d_inst", C.c_void_p), ("cap_inst", C.c_uint64), ("d_rows", C.c_void_p), ("cap_mem", C.c_uint64),
+        ("d_txn_off", C.c_void_p), ("d_txn", C.c_void_p), ("cap_txn", C.c_uint64),
+        ("d_tb", C.c_void_p), ("cap_tb", C.c_uint64), ("d_warp", C.c_void_p), ("cap_warp", C.c_uint64),
+        ("d_counters", C.c_void_p), ("d_status", C.c_void_p),
+    ]
+
+
+TI_NOALLOC_MAX_TEXT = 256 << 20
+
+
 class Command(C.Structure):
     _fields_ = [("kind", C.c_int32), ("line_off", C.c_uint32), ("line_len", C.c_uint32)]
 
@@ -67,7 +82,7 @@ SYMBOLS = [
     "ti_parse_kernel_header", "ti_kernel_open_file", "ti_kernel_open_buffer", "ti_kernel_open_device",
     "ti_kernel_close", "ti_kernel_upload", "ti_kernel_decode", "ti_kernel_sync", "ti_kernel_fetch",
     "ti_kernel_dev_view", "ti_kernel_counters", "ti_counters_add", "ti_counters_finalize", "ti_kernel_timing",
-    "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy",
+    "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc",
 ]
 
 
@@ -110,6 +125,7 @@ def load_library(path=None):
         "ti_plan_shards": (C.c_int, [V, S, C.c_int, P(S)]),
         "ti_parse_commandlist": (C.c_int, [V, S, P(Command), S, P(S)]),
         "ti_parse_memcpy": (C.c_int, [V, S, P(U64), P(U64)]),
+        "ti_decode_noalloc": (C.c_int, [V, P(NoAllocIO), V]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -128,5 +144,5 @@ def np_view(ptr, dtype, n, shape=None):
     return a.reshape(shape) if shape else a
 
 
-__all__ = ["load_library", "KernelHdr", "Counts", "View", "DevView", "Command", "TraceIngestError", "np_view",
+__all__ = ["load_library", "NoAllocIO", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "DevView", "Command", "TraceIngestError", "np_view",
            "SYMBOLS", "EF", "R"]

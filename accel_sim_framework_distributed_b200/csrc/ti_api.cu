@@ -455,3 +455,111 @@ static ti_status launch_decode(ti_kernel *k) {
   k->synced = false;
   return TI_OK;
 }
+
+// =====================================================================================
+// ti_decode_noalloc: the same fused decode, for callers that cannot let the library
+// allocate (see include/traceingest.h).  It has no counterpart in the reference.
+//
+// The only memory the decode needs beyond its inputs and outputs is the pair of
+// per-chunk look-back tables.  For this entry point they live in the file-scope device
+// array below instead of a cudaMalloc'ed buffer: (TI_NOALLOC_MAX_TEXT / chunk + 2)
+// entries of 32 + 8 bytes, about 0.65 MB, resident on every GPU that loads the library
+// for as long as the process lives.
+//
+// In host code the name `g_noalloc_scratch` is only a handle for the symbol, not an
+// address the GPU can use, so the device address is looked up once per device with
+// cudaGetSymbolAddress while that device is current and cached; kernels receive the
+// looked-up pointer.  That first call per device is the set-up: do it before any stream
+// capture starts.  All calls share the array.  Each call zeroes the entries it is about
+// to use (the tables must start at "nothing published") and leaves the rest as the last
+// call left them, so two calls whose GPU work can overlap would corrupt each other's
+// offsets -- serialise them.
+// =====================================================================================
+namespace {
+constexpr size_t kNoallocChunks = (size_t)(TI_NOALLOC_MAX_TEXT / ti::kChunk) + 2;
+constexpr size_t kNoallocBytes = kNoallocChunks * (sizeof(ti::State1) + sizeof(ti::State2));
+constexpr int kMaxDevices = 64;
+void *g_noalloc_addr[kMaxDevices];  // device address of the array, per device ordinal (0 = not looked up yet)
+}  // namespace
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocBytes];
+
+extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void *stream) {
+  if (!c || !io) return TI_ERR_INVALID_ARG;
+  if ((!io->d_text && io->len) || ((uintptr_t)io->d_text & 15)) { ti::set_error("d_text must be a 16-byte aligned device pointer"); return TI_ERR_INVALID_ARG; }
+  if (!io->d_inst || !io->d_rows || !io->d_txn_off || !io->d_txn || !io->d_tb || !io->d_warp || !io->d_counters || !io->d_status) {
+    ti::set_error("ti_decode_noalloc: every output pointer must be supplied by the caller");
+    return TI_ERR_INVALID_ARG;
+  }
+  if (io->len > TI_NOALLOC_MAX_TEXT) {
+    ti::set_error("ti_decode_noalloc: %llu bytes of text exceed the built-in scratch, which covers %llu bytes; cut the shard with ti_plan_shards",
+                  (unsigned long long)io->len, (unsigned long long)TI_NOALLOC_MAX_TEXT);
+    return TI_ERR_TOO_LARGE;
+  }
+  const int col = arch_column(io->binary_version);
+  if (col < 0) { ti::set_error("unsupported binary version: %u", io->binary_version); return TI_ERR_BINARY_VERSION; }
+  const ti_config &cfg = c->cfg;
+  const int dev = cfg.device;
+  if (dev < 0 || dev >= kMaxDevices) return TI_ERR_INVALID_ARG;
+  CK(cudaSetDevice(dev));
+  if (!g_noalloc_addr[dev]) {  // set-up, once per device, with that device current
+    void *p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    g_noalloc_addr[dev] = p;
+  }
+  cudaStream_t s = stream ? (cudaStream_t)stream : c->stream;
+  const uint32_t n_chunks = (uint32_t)((io->len + ti::kChunk - 1) / ti::kChunk);
+  unsigned char *scratch = (unsigned char *)g_noalloc_addr[dev];
+
+  ti::DecodeParams P;
+  memset(&P, 0, sizeof P);
+  P.text = (const uint8_t *)io->d_text;
+  P.len = io->len;
+  P.n_chunks = n_chunks;
+  P.trace_version = io->trace_version;
+  P.shmem_base = io->shmem_base_addr; P.local_base = io->local_base_addr;
+  P.inst = (ti_inst_rec *)io->d_inst; P.cap_inst = io->cap_inst;
+  P.rows = (uint64_t *)io->d_rows; P.cap_mem = io->cap_mem;
+  P.txn_off = (uint32_t *)io->d_txn_off;
+  P.txn = (ti_txn_rec *)io->d_txn; P.cap_txn = io->cap_txn;
+  P.tb = (ti_tb_rec *)io->d_tb; P.cap_tb = io->cap_tb;
+  P.warp = (ti_warp_rec *)io->d_warp; P.cap_warp = io->cap_warp;
+  P.state1 = (ti::State1 *)scratch;
+  P.state2 = (ti::State2 *)(scratch + kNoallocChunks * sizeof(ti::State1));
+  P.g = (ti::Globals *)io->d_status;
+  P.counters = (unsigned long long *)io->d_counters;
+  P.isa = c->d_isa[col]; P.spop = c->d_spop;
+  for (unsigned slot = 0; slot < 32; ++slot) {  // trace_driven.cc:441-480
+    const unsigned op = slot >= 18 ? 100 + (slot - 18) : slot;
+    const uint32_t *l = nullptr;
+    switch (op) {
+      case ti::OP_ALU: case ti::OP_INTP: case ti::OP_BRANCH: case ti::OP_CALL: case ti::OP_RET: l = cfg.lat_int; break;
+      case ti::OP_SP: l = cfg.lat_sp; break;
+      case ti::OP_DP: l = cfg.lat_dp; break;
+      case ti::OP_SFU: l = cfg.lat_sfu; break;
+      case ti::OP_TENSOR: l = cfg.lat_tensor; break;
+    }
+    if (op >= 100 && op < 108) l = cfg.lat_spec[op - 100];
+    P.lat[slot][0] = l ? (uint16_t)l[0] : 1; P.lat[slot][1] = l ? (uint16_t)l[1] : 1;
+  }
+  P.coalesce_arch = cfg.coalesce_arch; P.mem_warp_parts = cfg.mem_warp_parts; P.num_shmem_bank = cfg.num_shmem_bank;
+  P.shmem_limited_broadcast = cfg.shmem_limited_broadcast; P.gmem_skip_L1D = cfg.gmem_skip_L1D;
+
+  // what must start at zero: the table entries this call uses, the status block, the counters
+  CK(cudaMemsetAsync(P.state1, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s));
+  CK(cudaMemsetAsync(P.state2, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s));
+  CK(cudaMemsetAsync(io->d_status, 0, sizeof(ti::Globals), s));
+  CK(cudaMemsetAsync(io->d_counters, 0, sizeof(ti_counters), s));
+  CK(cudaMemsetAsync(io->d_txn_off, 0, 4, s));
+  if (n_chunks) {
+    const int grid = (int)std::min<uint32_t>((uint32_t)c->grid, n_chunks);
+#ifdef TI_EMU
+    emu::launch(dim3(grid), dim3(ti::kThreads), ti::kSmemBytes, [=]() { ti::ti_decode_kernel(P); });
+    emu::launch(dim3(2), dim3(256), 0, [=]() { ti::ti_check_kernel(P.warp, P.cap_warp, P.counters, P.g); });
+#else
+    ti::ti_decode_kernel<<<grid, ti::kThreads, ti::kSmemBytes, s>>>(P);
+    ti::ti_check_kernel<<<c->grid, 256, 0, s>>>(P.warp, P.cap_warp, P.counters, P.g);
+#endif
+    CK(cudaGetLastError());
+  }
+  return TI_OK;
+}
