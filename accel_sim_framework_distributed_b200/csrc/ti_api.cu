@@ -563,3 +563,12 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
   }
   return TI_OK;
 }
+
+#if defined(TI_PHASE_TIMING) && !defined(TI_EMU)
+// tuning builds only: read and reset the per-phase cycle sums
+extern "C" int ti_debug_phase_cycles(unsigned long long *out16) {
+  if (cudaMemcpyFromSymbol(out16, ti::g_phase_cycles, sizeof(unsigned long long) * 16) != cudaSuccess) return 1;
+  unsigned long long z[16] = {0};
+  return cudaMemcpyToSymbol(ti::g_phase_cycles, z, sizeof z) != cudaSuccess;
+}
+#endif

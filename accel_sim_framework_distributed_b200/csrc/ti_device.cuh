@@ -25,9 +25,17 @@
 #if defined(__CUDACC__) || defined(TI_EMU)
 #define TI_HD __host__ __device__ __forceinline__
 #define TI_D __device__ __forceinline__
+// rarely taken, register-hungry paths are kept out of line so that they do not set the
+// register budget of the whole kernel
+#ifdef TI_EMU
+#define TI_D_COLD inline
+#else
+#define TI_D_COLD __device__ __noinline__
+#endif
 #else
 #define TI_HD inline
 #define TI_D inline
+#define TI_D_COLD inline
 #endif
 
 namespace ti {
@@ -37,10 +45,13 @@ namespace ti {
 #define TI_CHUNK 16384
 #endif
 #ifndef TI_THREADS
-#define TI_THREADS 256
+#define TI_THREADS 320
 #endif
 #ifndef TI_TXN_STAGE
 #define TI_TXN_STAGE 768
+#endif
+#ifndef TI_TEXT_BUFS
+#define TI_TEXT_BUFS 2     // 2 = prefetch the next chunk's text during P7/P8; 1 = load at the top of the chunk
 #endif
 #ifndef TI_MIN_BLOCKS
 #define TI_MIN_BLOCKS 2   // resident CTAs per SM the register allocation is bounded for

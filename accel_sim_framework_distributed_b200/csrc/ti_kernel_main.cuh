@@ -4,6 +4,15 @@
 
 namespace ti {
 
+// Optional per-phase cycle accounting (tuning builds only, -DTI_PHASE_TIMING): thread 0 of
+// every CTA stamps clock64() at the phase boundaries and adds the deltas to a device array.
+#if defined(TI_PHASE_TIMING) && !defined(TI_EMU)
+__device__ unsigned long long g_phase_cycles[16];
+#define TI_STAMP(i) do { if (threadIdx.x == 0) { const long long t_ = clock64(); atomicAdd(&g_phase_cycles[i], (unsigned long long)(t_ - t_prev)); t_prev = t_; } } while (0)
+#else
+#define TI_STAMP(i) do { } while (0)
+#endif
+
 TI_D void flush_counters(uint32_t *cnt, unsigned long long *g) {
   for (int i = threadIdx.x; i < kSmCnt; i += kThreads) {
     const uint32_t v = cnt[i];
@@ -42,6 +51,9 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
   const unsigned tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   for (int i = tid; i < kSmCnt; i += kThreads) cnt[i] = 0;
   unsigned done_chunks = 0;
+#if defined(TI_PHASE_TIMING) && !defined(TI_EMU)
+  long long t_prev = clock64();
+#endif
 
   // ---- stage-in helpers.  Buffer offset j holds text byte (chunk * kChunk - 16 + j).  The
   // part of [0, 16 + kChunk + kSlack) that lies inside the shard on 16 B boundaries comes by
@@ -93,25 +105,22 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
 
   for (unsigned iter = 0;; ++iter) {
     __syncthreads();  // previous chunk fully drained; edge fills of this chunk's buffer visible
-    const unsigned buf = iter & 1;
+    const unsigned buf = TI_TEXT_BUFS == 2 ? (iter & 1) : 0u;
     const uint32_t chunk = ms->chunk_next;
     if (chunk >= P.n_chunks) break;
-    __syncthreads();  // everyone has read chunk_next
     if (tid == 0) {
-      // take the next ticket now and prefetch its text into the other buffer (free since the
-      // barrier above): tickets stay in file order, which is all the look-back needs
-      const uint32_t nxt = atomicAdd(&P.g->ticket, 1u);
-      ms->chunk_next = nxt;
-      if (nxt < P.n_chunks) issue_bulk(nxt, buf ^ 1);
       ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
+      if (TI_TEXT_BUFS == 1 && iter) issue_bulk(chunk, 0);   // single buffer: it is free only now
     }
+    if (TI_TEXT_BUFS == 1 && iter) fill_edges(chunk, 0);
     __syncthreads();
-    if (ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, buf ^ 1);
     uint8_t *text = smem + oText + buf * kTextBytes;
     uint4 *text_v = reinterpret_cast<uint4 *>(text);
     const uint64_t cb = (uint64_t)chunk * kChunk;            // text offset of the chunk
     const uint32_t tbase = (uint32_t)(cb - 16);              // text offset = tbase + smem offset (mod 2^32)
-    mbar_wait(&ms->mbar[buf], (iter >> 1) & 1);              // P0: this chunk's bulk copy has landed
+    TI_STAMP(0);   // top-of-loop bookkeeping, ticket, edge fills
+    mbar_wait(&ms->mbar[buf], TI_TEXT_BUFS == 2 ? ((iter >> 1) & 1) : (iter & 1));  // P0: this chunk's bulk copy has landed
+    TI_STAMP(1);
 
     // ---------------------------------------------------------------- P1 line index
     // A line start is a byte that follows '\n' and is not '\n' itself (blank lines
@@ -182,6 +191,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
     __syncthreads();
 
+    TI_STAMP(2);   // P1
     // ---------------------------------------------------------------- P2 tokenize
     for (uint32_t io = tid; io < n_inst; io += kThreads) {
       ti_inst_rec r;
@@ -198,6 +208,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
     __syncthreads();
 
+    TI_STAMP(3);   // P2
     // ---------------------------------------------------------------- P3 memory-instruction ordinals
     // low half: all memory instructions; high half: those taking the thread-per-instruction path
     const bool stride_path = P.mem_warp_parts == 1;
@@ -212,15 +223,14 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         });
     const uint32_t n_mem = p3 & 0xffff, n_fast = p3 >> 16, n_slow = n_mem - n_fast;
 
+    TI_STAMP(4);   // P3
     // ---------------------------------------------------------------- P4 look-back #1
-    if (wid == 0) {
+    uint64_t ex1[4];
+    {
       const uint32_t agg[4] = {n_inst, n_mem, n_tb, n_warp};
-      uint64_t ex[4];
-      lookback1(P.state1, chunk, agg, ex);
-      if (lane == 0) { ms->base_inst = ex[0]; ms->base_mem = ex[1]; ms->base_tb = ex[2]; ms->base_warp = ex[3]; }
+      cta_lookback1(P.state1, chunk, agg, ex1, ms->lb);
     }
-    __syncthreads();
-    const uint64_t base_inst = ms->base_inst, base_mem = ms->base_mem, base_tb = ms->base_tb, base_warp = ms->base_warp;
+    const uint64_t base_inst = ex1[0], base_mem = ex1[1], base_tb = ex1[2], base_warp = ex1[3];
     if (tid == 0) {
       uint32_t ov = 0;
       if (base_inst + n_inst > P.cap_inst) ov |= 1;
@@ -231,6 +241,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       if (ov) atomicOr(&P.g->overflow, ov);
     }
 
+    TI_STAMP(5);   // P4
     // ---------------------------------------------------------------- P5 structural lines
     // ordinals of "thread block" (low half) and "warp" (high half) lines among the structural lines
     block_scan(
@@ -278,6 +289,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
           note_error(ms, fl, tbase + (uint32_t)o);
         });
 
+    TI_STAMP(6);   // P5
     // ---------------------------------------------------------------- P6a base+stride: thread per instruction
     for (uint32_t fo = tid; fo < n_fast; fo += kThreads) {
       const uint32_t mo = fast_list[fo];
@@ -314,6 +326,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     __syncthreads();
     const uint32_t n_warp_path = n_slow + ms->n_extra;
 
+    TI_STAMP(7);   // P6a
     // ---------------------------------------------------------------- P6b everything else: warp per instruction
     for (;;) {
       uint32_t so = 0;
@@ -373,16 +386,23 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
     __syncthreads();
 
+    TI_STAMP(8);   // P6b
+    // Take the next ticket only now and prefetch that chunk's text into the other buffer (free
+    // since the top-of-loop barrier) while P7/P8 run.  Taking it any earlier would hand out
+    // tickets a whole chunk time before the work starts, so a chunk's predecessor could begin
+    // later than the chunk itself and the look-back would wait for it.
+    if (tid == 0) {
+      const uint32_t nxt = atomicAdd(&P.g->ticket, 1u);
+      ms->chunk_next = nxt;
+      if (TI_TEXT_BUFS == 2 && nxt < P.n_chunks) issue_bulk(nxt, buf ^ 1);
+    }
     // ---------------------------------------------------------------- P7 look-back #2 + ordered copy-out
     const uint32_t n_txn_chunk = block_scan(
         n_mem, ms->warp_tot, [&](uint32_t i) { return (uint32_t)txn_cnt[i]; },
         [&](uint32_t i, uint32_t ex, uint32_t) { txn_loc[i] = (uint16_t)ex; });
-    if (wid == 0) {
-      const uint64_t ex = lookback2(P.state2, chunk, n_txn_chunk);
-      if (lane == 0) ms->base_txn = ex;
-    }
-    __syncthreads();
-    const uint64_t base_txn = ms->base_txn;
+    const uint64_t base_txn = cta_lookback2(P.state2, chunk, n_txn_chunk, ms->lb);
+    TI_STAMP(9);   // P7 scan + look-back #2
+    if (TI_TEXT_BUFS == 2 && ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, buf ^ 1);   // visible after the barriers above
     if (tid == 0) {
       uint32_t ov = 0;
       if (base_txn + n_txn_chunk > P.cap_txn) ov |= 4;
@@ -431,6 +451,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       }
     }
 
+    TI_STAMP(10);  // P7 copy-out
     // ---------------------------------------------------------------- P8 records out + counters
     {
       const uint4 *src = reinterpret_cast<const uint4 *>(recs);
@@ -454,6 +475,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       atomicOr(&P.g->error_flags, ms->err);
       atomicMin(&P.g->first_error_off, ms->first_err);
     }
+    TI_STAMP(11);  // P8
     if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }
   }
   __syncthreads();

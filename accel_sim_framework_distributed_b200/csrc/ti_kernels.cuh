@@ -32,16 +32,18 @@ static inline unsigned __vcmpeq4(unsigned a, unsigned b) {
 namespace ti {
 
 // ------------------------------------------------------------ shared-memory plan
+struct LbWarp { uint32_t L; uint32_t s[4]; unsigned long long i0, i1; };  // see cta_lookback1
 struct Misc {
   uint64_t base_inst, base_mem, base_tb, base_warp, base_txn;
   uint64_t warp_tot[kWarps];
   uint32_t chunk, n_inst, n_sl, n_mem, n_tb, n_warp, n_txn;
   uint32_t next_mem, stage_used, err, first_err, n_extra, chunk_next;
   uint64_t mbar[2];  // one mbarrier per text buffer (completion of the bulk copy)
+  LbWarp lb[kWarps];  // per-warp partial results of the CTA-wide look-back
 };
 constexpr int align16(int x) { return (x + 15) & ~15; }
 constexpr int oText = 0;                                     // two text buffers: the chunk being decoded + the prefetched next one
-constexpr int oRecs = oText + 2 * kTextBytes;
+constexpr int oRecs = oText + TI_TEXT_BUFS * kTextBytes;
 constexpr int oStage = oRecs + kRecCap * 32;
 constexpr int oInstOff = oStage + kTxnStage * 32;            // u16[kRecCap]  smem offset of each instruction line
 constexpr int oSlOff = oInstOff + align16(kRecCap * 2);      // u16[kSlCap]   smem offset of each structural line
@@ -170,6 +172,87 @@ TI_D uint64_t lookback2(State2 *st, uint32_t c, uint32_t agg) {
     if (L < 32) { excl += __shfl_sync(kFull, W, L) & 0x3fffffffffffffffull; break; }
   }
   if (lane == 0) st_vol64(&st[c].w, kValid | (excl + agg));
+  return excl;
+}
+
+// ---- CTA-wide variants: thread t inspects chunk c-1-t, so one round covers kThreads
+// predecessors.  The persistent CTAs run phase-locked (equal work per chunk), so a chunk's
+// predecessors publish their aggregates at about the same moment as the chunk itself and
+// their inclusive prefixes only after their own look-back: the nearest inclusive prefix is
+// typically ~100 chunks back.  A single warp needed several dependent 32-wide rounds of L2
+// round trips for that (measured: 20% of the kernel); the whole CTA needs one.
+
+TI_D void cta_lookback1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64_t (&excl)[4], LbWarp *lb) {
+  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
+  if (threadIdx.x == 0)
+    st_vol64(&st[c].agg, kValid | (unsigned long long)agg[3] << 42 | (unsigned long long)agg[2] << 28 |
+                             (unsigned long long)agg[1] << 14 | agg[0]);
+  excl[0] = excl[1] = excl[2] = excl[3] = 0;
+  for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= kThreads) {
+    const int64_t j = idx - (int64_t)threadIdx.x;
+    unsigned long long A = kValid, I0 = kValid, I1 = kValid;
+    for (;;) {
+      if (j >= 0) { I0 = ld_vol64(&st[j].inc0); I1 = ld_vol64(&st[j].inc1); A = ld_vol64(&st[j].agg); }
+      if (__syncthreads_and((int)((((I0 & I1) | A) >> 63) & 1))) break;
+      __nanosleep(64);
+    }
+    const bool hasinc = (I0 & I1) >> 63;
+    const uint32_t have = __ballot_sync(kFull, hasinc);
+    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
+    const bool useagg = lane < L;
+    const uint32_t s0 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A & 0x3fff) : 0u);
+    const uint32_t s1 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 14 & 0x3fff) : 0u);
+    const uint32_t s2 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 28 & 0x3fff) : 0u);
+    const uint32_t s3 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 42 & 0x3fff) : 0u);
+    const unsigned long long i0 = __shfl_sync(kFull, I0, L & 31), i1 = __shfl_sync(kFull, I1, L & 31);
+    if (lane == 0) { lb[w].L = L; lb[w].s[0] = s0; lb[w].s[1] = s1; lb[w].s[2] = s2; lb[w].s[3] = s3; lb[w].i0 = i0; lb[w].i1 = i1; }
+    __syncthreads();
+    bool found = false;
+    for (unsigned k = 0; k < (unsigned)kWarps && !found; ++k) {   // warp k looked at nearer chunks than warp k+1
+      excl[0] += lb[k].s[0]; excl[1] += lb[k].s[1]; excl[2] += lb[k].s[2]; excl[3] += lb[k].s[3];
+      if (lb[k].L < 32) {
+        const unsigned long long a0 = lb[k].i0, a1 = lb[k].i1;
+        excl[0] += a0 & 0x7fffffffull; excl[1] += a0 >> 31 & 0x7fffffffull;
+        excl[2] += a1 & 0x7fffffffull; excl[3] += a1 >> 31 & 0x7fffffffull;
+        found = true;
+      }
+    }
+    __syncthreads();   // lb is reused by the next round / the next look-back
+    if (found) break;
+  }
+  if (threadIdx.x == 0) {
+    st_vol64(&st[c].inc0, kValid | (excl[1] + agg[1]) << 31 | (excl[0] + agg[0]));
+    st_vol64(&st[c].inc1, kValid | (excl[3] + agg[3]) << 31 | (excl[2] + agg[2]));
+  }
+}
+
+TI_D uint64_t cta_lookback2(State2 *st, uint32_t c, uint32_t agg, LbWarp *lb) {
+  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
+  if (threadIdx.x == 0 && c) st_vol64(&st[c].w, kAggValid | agg);
+  uint64_t excl = 0;
+  for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= kThreads) {
+    const int64_t j = idx - (int64_t)threadIdx.x;
+    unsigned long long W = kValid;
+    for (;;) {
+      if (j >= 0) W = ld_vol64(&st[j].w);
+      if (__syncthreads_and((int)((W >> 62) != 0))) break;
+      __nanosleep(64);
+    }
+    const uint32_t have = __ballot_sync(kFull, (W >> 63) != 0);
+    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
+    const uint32_t s0 = __reduce_add_sync(kFull, lane < L ? (uint32_t)(W & 0xffffffffull) : 0u);
+    const unsigned long long i0 = __shfl_sync(kFull, W, L & 31);
+    if (lane == 0) { lb[w].L = L; lb[w].s[0] = s0; lb[w].i0 = i0; }
+    __syncthreads();
+    bool found = false;
+    for (unsigned k = 0; k < (unsigned)kWarps && !found; ++k) {
+      excl += lb[k].s[0];
+      if (lb[k].L < 32) { excl += lb[k].i0 & 0x3fffffffffffffffull; found = true; }
+    }
+    __syncthreads();
+    if (found) break;
+  }
+  if (threadIdx.x == 0) st_vol64(&st[c].w, kValid | (excl + agg));
   return excl;
 }
 

@@ -78,7 +78,7 @@ TI_D ti_txn_rec reduce_and_send(const Txn &t, unsigned seg, unsigned type, unsig
 
 // ---- address decompression.  `q` = smem offset of the first token after the mode
 // field; tokpos = 33 u16 of per-warp scratch.  Returns this lane's address.
-TI_D uint64_t decode_addresses(const uint8_t *text, unsigned q, unsigned mode, uint32_t mask, uint16_t *tokpos,
+TI_D_COLD uint64_t decode_addresses(const uint8_t *text, unsigned q, unsigned mode, uint32_t mask, uint16_t *tokpos,
                                uint32_t &flags) {
   const unsigned lane = lane_id();
   const bool active = mask >> lane & 1;
@@ -286,7 +286,7 @@ TI_D unsigned stride_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsign
 }
 
 // ---- shared-memory bank conflicts: returns `cycles` (warp-uniform)
-TI_D unsigned shared_cycles(const DecodeParams &P, uint32_t mask, uint64_t addr) {
+TI_D_COLD unsigned shared_cycles(const DecodeParams &P, uint32_t mask, uint64_t addr) {
   const unsigned lane = lane_id();
   const unsigned parts = (unsigned)P.mem_warp_parts, sub = 32 / parts;
   const uint64_t word = addr & ~3ull;
@@ -340,7 +340,7 @@ TI_D unsigned shared_cycles(const DecodeParams &P, uint32_t mask, uint64_t addr)
 // small per-warp smem scratch; the others ("pure B") are transactions of their own.
 // Outputs: out[0]/pos[0] = this lane's A-group if it leads one, out[1]/pos[1] = its pure
 // B-group; pos = ~0u when absent.  Returns the number of transactions.
-TI_D unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_t addr, unsigned ds, unsigned seg,
+TI_D_COLD unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_t addr, unsigned ds, unsigned seg,
                               Txn out[2], unsigned pos[2], uint32_t *scratch) {
   const unsigned lane = lane_id();
   const unsigned parts = (unsigned)P.mem_warp_parts, sub = 32 / parts;
@@ -422,7 +422,7 @@ TI_D unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_t add
 // ---- atomics: order-dependent first fit per block (abstract_hardware_model.cc:626-673).
 // Transaction k lives in lane k; `pos` receives its emit position.  Returns the count,
 // or sets TI_EF_ATOMIC_STRADDLE.
-TI_D unsigned coalesce_atomic(const DecodeParams &P, uint32_t mask, uint64_t addr, unsigned ds, unsigned seg, Txn &mine,
+TI_D_COLD unsigned coalesce_atomic(const DecodeParams &P, uint32_t mask, uint64_t addr, unsigned ds, unsigned seg, Txn &mine,
                               unsigned &pos, uint32_t &flags) {
   const unsigned lane = lane_id();
   const unsigned parts = (unsigned)P.mem_warp_parts, sub = 32 / parts;

@@ -179,3 +179,16 @@ void __syncthreads() {
   }
   while (c.bar_gen == gen) emu::yield_();
 }
+
+// barrier + AND-reduction of a predicate over the CTA (three plain barriers: vote, read, reset)
+int __syncthreads_and(int pred) {
+  emu::Machine &m = emu::M();
+  emu::Cta &c = m.ctas[m.cur->cta];
+  if (!pred) c.and_acc = 0;
+  __syncthreads();
+  const int r = c.and_acc;
+  __syncthreads();
+  if (m.cur->tid == 0) c.and_acc = 1;
+  __syncthreads();
+  return r;
+}

@@ -55,6 +55,7 @@ struct Cta {
   std::vector<unsigned char> smem;
   std::vector<Warp> warps;
   unsigned bar_count = 0, bar_gen = 0, live = 0;
+  int and_acc = 1;
 };
 
 struct Thread {
@@ -87,6 +88,7 @@ extern dim3 blockDim, gridDim;
 
 // ------------------------------------------------------------ synchronisation
 void __syncthreads();
+int __syncthreads_and(int pred);
 static inline void __syncwarp(unsigned mask = 0xffffffffu) { emu::collective(mask, emu::SYNCWARP, 0, 0); }
 static inline void __threadfence() {}
 static inline void __threadfence_block() {}
