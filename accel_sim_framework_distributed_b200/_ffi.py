@@ -82,7 +82,7 @@ SYMBOLS = [
     "ti_parse_kernel_header", "ti_kernel_open_file", "ti_kernel_open_buffer", "ti_kernel_open_device",
     "ti_kernel_close", "ti_kernel_upload", "ti_kernel_decode", "ti_kernel_sync", "ti_kernel_fetch",
     "ti_kernel_dev_view", "ti_kernel_counters", "ti_counters_add", "ti_counters_finalize", "ti_kernel_timing",
-    "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc",
+    "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
 ]
 
 
@@ -126,6 +126,7 @@ def load_library(path=None):
         "ti_parse_commandlist": (C.c_int, [V, S, P(Command), S, P(S)]),
         "ti_parse_memcpy": (C.c_int, [V, S, P(U64), P(U64)]),
         "ti_decode_noalloc": (C.c_int, [V, P(NoAllocIO), V]),
+        "ti_kernel_decode_streamed": (C.c_int, [V, S, P(View)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

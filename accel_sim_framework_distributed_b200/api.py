@@ -112,6 +112,26 @@ class KernelTrace:
         self._next_tb = 0
         return self._decoded
 
+    def run_streamed(self, shard_bytes=0, check=True):
+        """The whole host -> host path with copies and kernel overlapped (ti_kernel_decode_streamed)."""
+        view = _ffi.View()
+        st = self._p.lib.ti_kernel_decode_streamed(self._h, shard_bytes, C.byref(view))
+        if st != 0 and (check or st != _ffi.TI_ERR_PARSE):
+            self._p._ck(st)
+        if st != 0:
+            return None
+        self._range = (0, self.body_len)
+        d = Decoded(view, self.body_len)
+        cnt = np.zeros(1, dtype=R.COUNTERS)
+        self._p._ck(self._p.lib.ti_kernel_counters(self._h, cnt.ctypes.data))
+        d.counters = cnt[0]
+        pw = np.zeros(1, dtype=R.POWER)
+        self._p._ck(self._p.lib.ti_counters_finalize(self._p.ctx, cnt.ctypes.data, pw.ctypes.data))
+        d.power = pw[0]
+        self._decoded = d
+        self._next_tb = 0
+        return d
+
     def close(self):
         if self._h:
             self._p.lib.ti_kernel_close(self._h)

@@ -86,8 +86,13 @@ struct ti_ctx {
   int grid = 0;
 };
 
+struct ti_stream_state;
+static void stream_state_free(ti_stream_state *ss);
+
 struct ti_kernel {
   ti_ctx *ctx = nullptr;
+  ti_stream_state *streams = nullptr;   // ti_kernel_decode_streamed: streams, events, two device buffer sets
+  bool streamed = false;
   ti_kernel_hdr hdr;
   int col = -1;
   const char *h_body = nullptr;   // host body (owned pinned file image or borrowed)
@@ -242,6 +247,7 @@ ti_status ti_kernel_open_device(ti_ctx *ctx, const void *d_body, size_t len, con
 void ti_kernel_close(ti_kernel *k) {
   if (!k) return;
   cudaStreamSynchronize(k->ctx->stream);
+  stream_state_free(k->streams);
   DevBuf *d[] = {&k->d_text, &k->inst, &k->rows, &k->txn_off, &k->txn, &k->tb, &k->warp, &k->state1, &k->state2, &k->globals, &k->counters};
   for (DevBuf *b : d) b->release();
   HostBuf *h[] = {&k->h_file, &k->h_inst, &k->h_rows, &k->h_txn_off, &k->h_txn, &k->h_tb, &k->h_warp, &k->h_small};
@@ -253,7 +259,7 @@ ti_status ti_kernel_upload(ti_kernel *k, size_t begin, size_t end) {
   if (k && end == (size_t)-1) end = k->body_len;
   if (!k || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
   if (end - begin > 0xfffffff0ull) { ti::set_error("shard of %zu bytes: cut it with ti_plan_shards", end - begin); return TI_ERR_TOO_LARGE; }
-  k->decoded = k->synced = k->retried = false;
+  k->decoded = k->synced = k->retried = k->streamed = false;
   if (k->d_borrowed) {
     if (begin & 15) { ti::set_error("device-resident shards must start 16-byte aligned"); return TI_ERR_INVALID_ARG; }
     k->sh_begin = begin; k->sh_len = end - begin; k->uploaded = true;
@@ -325,6 +331,14 @@ ti_status ti_kernel_sync(ti_kernel *k, ti_counts *counts) {
 ti_status ti_kernel_fetch(ti_kernel *k, ti_view *v) {
   if (!k || !v) return TI_ERR_INVALID_ARG;
   if (!k->synced) { ti::set_error("ti_kernel_fetch before a successful ti_kernel_sync"); return TI_ERR_STATE; }
+  if (k->streamed) {  // ti_kernel_decode_streamed already brought everything to the host
+    v->text = k->h_body;
+    v->inst = (const ti_inst_rec *)k->h_inst.p; v->addr_rows = (const uint64_t *)k->h_rows.p;
+    v->txn_off = (const uint32_t *)k->h_txn_off.p; v->txn = (const ti_txn_rec *)k->h_txn.p;
+    v->tb = (const ti_tb_rec *)k->h_tb.p; v->warp = (const ti_warp_rec *)k->h_warp.p;
+    v->counts = k->counts;
+    return TI_OK;
+  }
   cudaStream_t s = k->ctx->stream;
   const ti_counts &n = k->counts;
   ti_status st;
@@ -453,6 +467,254 @@ static ti_status launch_decode(ti_kernel *k) {
   CK(cudaEventRecord(c->ev1, s));
   k->decoded = true;
   k->synced = false;
+  return TI_OK;
+}
+
+// =====================================================================================
+// ti_kernel_decode_streamed: host text -> host results with the copies overlapped.
+//
+// The body is cut into shards at "#BEGIN_TB" (ti_plan_shards).  Three streams run a
+// software pipeline over them with two device buffer sets:
+//     H2D(i+1)  ||  decode(i)  ||  D2H(i-1)
+// PCIe is full duplex, so the text going up and the records coming down share the link;
+// the end-to-end time approaches max(H2D, D2H) instead of their sum.  The kernel is told
+// what the preceding shards produced (DecodeParams::off_*), so every index and text
+// offset it stores is already file-global and the host arrays are a plain concatenation.
+// =====================================================================================
+namespace {
+
+struct StreamSet {
+  DevBuf text, inst, rows, txn_off, txn, tb, warp, state1, state2, globals, counters;
+  HostBuf small;                           // Globals + ti_counters of the shard
+  cudaEvent_t ev_h2d = nullptr, ev_dec = nullptr, ev_d2h = nullptr, t0 = nullptr, t1 = nullptr;
+};
+
+struct StreamState {
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  StreamSet set[2];
+  bool ready = false;
+};
+
+void fill_model_params(ti::DecodeParams &P, const ti_ctx *c, int col, const ti_kernel_hdr &hdr) {
+  const ti_config &cfg = c->cfg;
+  P.trace_version = hdr.trace_version;
+  P.shmem_base = hdr.shmem_base_addr; P.local_base = hdr.local_base_addr;
+  P.isa = c->d_isa[col]; P.spop = c->d_spop;
+  for (unsigned slot = 0; slot < 32; ++slot) {  // trace_driven.cc:441-480
+    const unsigned op = slot >= 18 ? 100 + (slot - 18) : slot;
+    const uint32_t *l = nullptr;
+    switch (op) {
+      case ti::OP_ALU: case ti::OP_INTP: case ti::OP_BRANCH: case ti::OP_CALL: case ti::OP_RET: l = cfg.lat_int; break;
+      case ti::OP_SP: l = cfg.lat_sp; break;
+      case ti::OP_DP: l = cfg.lat_dp; break;
+      case ti::OP_SFU: l = cfg.lat_sfu; break;
+      case ti::OP_TENSOR: l = cfg.lat_tensor; break;
+    }
+    if (op >= 100 && op < 108) l = cfg.lat_spec[op - 100];
+    P.lat[slot][0] = l ? (uint16_t)l[0] : 1; P.lat[slot][1] = l ? (uint16_t)l[1] : 1;
+  }
+  P.coalesce_arch = cfg.coalesce_arch; P.mem_warp_parts = cfg.mem_warp_parts; P.num_shmem_bank = cfg.num_shmem_bank;
+  P.shmem_limited_broadcast = cfg.shmem_limited_broadcast; P.gmem_skip_L1D = cfg.gmem_skip_L1D;
+}
+
+}  // namespace
+
+struct ti_stream_state : StreamState {};
+
+static void stream_state_free(ti_stream_state *ss) {
+  if (!ss) return;
+  for (StreamSet &t : ss->set) {
+    DevBuf *d[] = {&t.text, &t.inst, &t.rows, &t.txn_off, &t.txn, &t.tb, &t.warp, &t.state1, &t.state2, &t.globals, &t.counters};
+    for (DevBuf *b : d) b->release();
+    t.small.release();
+    cudaEvent_t *e[] = {&t.ev_h2d, &t.ev_dec, &t.ev_d2h, &t.t0, &t.t1};
+    for (cudaEvent_t *x : e) if (*x) cudaEventDestroy(*x);
+  }
+  if (ss->s_h2d) cudaStreamDestroy(ss->s_h2d);
+  if (ss->s_d2h) cudaStreamDestroy(ss->s_d2h);
+  delete ss;
+}
+
+extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes, ti_view *v) {
+  if (!k || !v) return TI_ERR_INVALID_ARG;
+  if (!k->h_body && k->body_len) { ti::set_error("ti_kernel_decode_streamed needs a host-resident body"); return TI_ERR_STATE; }
+  if (k->body_len > 0xfffffff0ull) { ti::set_error("body of %zu bytes: opcode offsets are 32 bit", k->body_len); return TI_ERR_TOO_LARGE; }
+  ti_ctx *c = k->ctx;
+  const ti_config &cfg = c->cfg;
+  if (!shard_bytes) shard_bytes = (size_t)64 << 20;
+  const int n_sh = (int)std::max<size_t>(1, (k->body_len + shard_bytes - 1) / shard_bytes);
+  std::vector<size_t> cuts(n_sh + 1);
+  ti_status st = ti_plan_shards(k->h_body, k->body_len, n_sh, cuts.data());
+  if (st != TI_OK) return st;
+  size_t max_len = 0;
+  for (int i = 0; i < n_sh; ++i) max_len = std::max(max_len, cuts[i + 1] - cuts[i]);
+
+  if (!k->streams) k->streams = new ti_stream_state;
+  ti_stream_state *ss = k->streams;
+  if (!ss->ready) {
+    CK(cudaStreamCreateWithFlags(&ss->s_h2d, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&ss->s_d2h, cudaStreamNonBlocking));
+    for (StreamSet &t : ss->set) {
+      CK(cudaEventCreate(&t.ev_h2d)); CK(cudaEventCreate(&t.ev_dec)); CK(cudaEventCreate(&t.ev_d2h));
+      CK(cudaEventCreate(&t.t0)); CK(cudaEventCreate(&t.t1));
+    }
+    ss->ready = true;
+  }
+  // per-shard device capacities (same per-byte defaults as ti_kernel_decode)
+  const double L = (double)max_len;
+  const uint64_t cap_inst = (uint64_t)(L * (cfg.cap_inst_per_byte > 0 ? cfg.cap_inst_per_byte : 1.0 / 24)) + ti::kRecCap;
+  const uint64_t cap_mem = (uint64_t)(L * (cfg.cap_mem_per_byte > 0 ? cfg.cap_mem_per_byte : 1.0 / 32)) + ti::kRecCap;
+  const uint64_t cap_txn = (uint64_t)(L * (cfg.cap_txn_per_byte > 0 ? cfg.cap_txn_per_byte : 1.0 / 8)) + 4096;
+  const uint64_t cap_tb = (uint64_t)(L / 40) + 64, cap_warp = (uint64_t)(L / 19) + 64;
+  const uint32_t max_chunks = (uint32_t)((max_len + ti::kChunk - 1) / ti::kChunk);
+  for (StreamSet &t : ss->set) {
+    if ((st = t.text.ensure(((max_len + 15) & ~(size_t)15) + 16)) != TI_OK) return st;
+    if ((st = t.inst.ensure(cap_inst * sizeof(ti_inst_rec))) != TI_OK) return st;
+    if ((st = t.rows.ensure(cap_mem * 256)) != TI_OK) return st;
+    if ((st = t.txn_off.ensure((cap_mem + 1) * 4)) != TI_OK) return st;
+    if ((st = t.txn.ensure(cap_txn * sizeof(ti_txn_rec))) != TI_OK) return st;
+    if ((st = t.tb.ensure(cap_tb * sizeof(ti_tb_rec))) != TI_OK) return st;
+    if ((st = t.warp.ensure(cap_warp * sizeof(ti_warp_rec))) != TI_OK) return st;
+    if ((st = t.state1.ensure((size_t)(max_chunks + 1) * sizeof(ti::State1))) != TI_OK) return st;
+    if ((st = t.state2.ensure((size_t)(max_chunks + 1) * sizeof(ti::State2))) != TI_OK) return st;
+    if ((st = t.globals.ensure(sizeof(ti::Globals))) != TI_OK) return st;
+    if ((st = t.counters.ensure(sizeof(ti_counters))) != TI_OK) return st;
+    if ((st = t.small.ensure(sizeof(ti::Globals) + sizeof(ti_counters))) != TI_OK) return st;
+  }
+
+  cudaStream_t s_c = c->stream, s_up = ss->s_h2d, s_dn = ss->s_d2h;
+  auto h2d = [&](int i) -> ti_status {   // text of shard i -> its buffer set
+    StreamSet &t = ss->set[i & 1];
+    const size_t n = cuts[i + 1] - cuts[i];
+    if (i >= 2) CK(cudaStreamWaitEvent(s_up, t.ev_dec, 0));   // decode(i-2) has finished reading this buffer
+    if (n) CK(cudaMemcpyAsync(t.text.p, k->h_body + cuts[i], n, cudaMemcpyHostToDevice, s_up));
+    CK(cudaEventRecord(t.ev_h2d, s_up));
+    return TI_OK;
+  };
+
+  uint64_t T_inst = 0, T_mem = 0, T_txn = 0, T_tb = 0, T_warp = 0;
+  ti_counters total;
+  memset(&total, 0, sizeof total);
+  uint32_t flags = 0, first_err = 0xffffffffu;
+  float ms_sum = 0;
+  bool overflow = false;
+  if ((st = h2d(0)) != TI_OK) return st;
+  if (n_sh > 1 && (st = h2d(1)) != TI_OK) return st;
+  for (int i = 0; i < n_sh && !overflow; ++i) {
+    StreamSet &t = ss->set[i & 1];
+    const size_t len = cuts[i + 1] - cuts[i];
+    const uint32_t n_chunks = (uint32_t)((len + ti::kChunk - 1) / ti::kChunk);
+    ti::DecodeParams P;
+    memset(&P, 0, sizeof P);
+    fill_model_params(P, c, k->col, k->hdr);
+    P.text = (const uint8_t *)t.text.p; P.len = len; P.n_chunks = n_chunks;
+    P.inst = (ti_inst_rec *)t.inst.p; P.cap_inst = cap_inst;
+    P.rows = (uint64_t *)t.rows.p; P.cap_mem = cap_mem;
+    P.txn_off = (uint32_t *)t.txn_off.p;
+    P.txn = (ti_txn_rec *)t.txn.p; P.cap_txn = cap_txn;
+    P.tb = (ti_tb_rec *)t.tb.p; P.cap_tb = cap_tb;
+    P.warp = (ti_warp_rec *)t.warp.p; P.cap_warp = cap_warp;
+    P.state1 = (ti::State1 *)t.state1.p; P.state2 = (ti::State2 *)t.state2.p;
+    P.g = (ti::Globals *)t.globals.p; P.counters = (unsigned long long *)t.counters.p;
+    P.off_inst = T_inst; P.off_mem = T_mem; P.off_txn = T_txn; P.off_warp = T_warp; P.off_text = cuts[i];
+
+    CK(cudaStreamWaitEvent(s_c, t.ev_h2d, 0));
+    if (i >= 2) CK(cudaStreamWaitEvent(s_c, t.ev_d2h, 0));    // D2H(i-2) has drained this set's outputs
+    CK(cudaEventRecord(t.t0, s_c));
+    CK(cudaMemsetAsync(t.state1.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s_c));
+    CK(cudaMemsetAsync(t.state2.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s_c));
+    CK(cudaMemsetAsync(t.globals.p, 0, sizeof(ti::Globals), s_c));
+    CK(cudaMemsetAsync(t.counters.p, 0, sizeof(ti_counters), s_c));
+    CK(cudaMemsetAsync(t.txn_off.p, 0, 4, s_c));
+    if (n_chunks) {
+      const int grid = (int)std::min<uint32_t>((uint32_t)c->grid, n_chunks);
+#ifdef TI_EMU
+      emu::launch(dim3(grid), dim3(ti::kThreads), ti::kSmemBytes, [=]() { ti::ti_decode_kernel(P); });
+      emu::launch(dim3(2), dim3(256), 0, [=]() { ti::ti_check_kernel(P.warp, P.cap_warp, P.counters, P.g, P.off_inst); });
+#else
+      ti::ti_decode_kernel<<<grid, ti::kThreads, ti::kSmemBytes, s_c>>>(P);
+      ti::ti_check_kernel<<<c->grid, 256, 0, s_c>>>(P.warp, P.cap_warp, P.counters, P.g, P.off_inst);
+#endif
+      CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(t.t1, s_c));
+    ti::Globals *g = (ti::Globals *)t.small.p;
+    ti_counters *hc = (ti_counters *)((char *)t.small.p + sizeof(ti::Globals));
+    CK(cudaMemcpyAsync(g, t.globals.p, sizeof(ti::Globals), cudaMemcpyDeviceToHost, s_c));
+    CK(cudaMemcpyAsync(hc, t.counters.p, sizeof(ti_counters), cudaMemcpyDeviceToHost, s_c));
+    CK(cudaEventRecord(t.ev_dec, s_c));
+    if (i + 2 < n_sh && (st = h2d(i + 2)) != TI_OK) return st;  // queued behind ev_dec of this set
+    CK(cudaEventSynchronize(t.ev_dec));                         // the shard's counts are on the host now
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, t.t0, t.t1));
+    ms_sum += ms;
+    if (g->overflow) { overflow = true; break; }
+    flags |= g->error_flags;
+    if (g->error_flags && g->first_error_off < first_err) first_err = g->first_error_off + (uint32_t)cuts[i];
+    // host arrays: grow when the running totals no longer fit (first shard: extrapolate)
+    const double scale = 1.15 * (double)k->body_len / (double)std::max<size_t>(1, cuts[i + 1]);
+    struct { HostBuf *b; uint64_t have, add; size_t elt; } need[] = {
+        {&k->h_inst, T_inst, hc->n_inst, sizeof(ti_inst_rec)}, {&k->h_rows, T_mem, hc->n_mem, 256},
+        {&k->h_txn_off, T_mem, hc->n_mem + 1, 4},               {&k->h_txn, T_txn, hc->n_txn, sizeof(ti_txn_rec)},
+        {&k->h_tb, T_tb, hc->n_tb, sizeof(ti_tb_rec)},          {&k->h_warp, T_warp, hc->n_warp, sizeof(ti_warp_rec)}};
+    for (auto &nd : need) {
+      const size_t want = (size_t)(nd.have + nd.add) * nd.elt;
+      if (want <= nd.b->bytes) continue;
+      CK(cudaStreamSynchronize(s_dn));                          // copies into the old buffer are done
+      HostBuf bigger;
+      if ((st = bigger.ensure((size_t)((double)want * scale) + 4096)) != TI_OK) return st;
+      if (nd.have) memcpy(bigger.p, nd.b->p, (size_t)nd.have * nd.elt);
+      nd.b->release();
+      *nd.b = bigger;
+    }
+    // results of shard i -> host, behind its decode
+    CK(cudaStreamWaitEvent(s_dn, t.ev_dec, 0));
+    auto down = [&](HostBuf &h, uint64_t at, const DevBuf &d, uint64_t n, size_t elt) -> ti_status {
+      if (n) CK(cudaMemcpyAsync((char *)h.p + at * elt, d.p, n * elt, cudaMemcpyDeviceToHost, s_dn));
+      return TI_OK;
+    };
+    if ((st = down(k->h_inst, T_inst, t.inst, hc->n_inst, sizeof(ti_inst_rec))) != TI_OK) return st;
+    if ((st = down(k->h_rows, T_mem, t.rows, hc->n_mem, 256)) != TI_OK) return st;
+    if ((st = down(k->h_txn_off, T_mem, t.txn_off, hc->n_mem + 1, 4)) != TI_OK) return st;
+    if ((st = down(k->h_txn, T_txn, t.txn, hc->n_txn, sizeof(ti_txn_rec))) != TI_OK) return st;
+    if ((st = down(k->h_tb, T_tb, t.tb, hc->n_tb, sizeof(ti_tb_rec))) != TI_OK) return st;
+    if ((st = down(k->h_warp, T_warp, t.warp, hc->n_warp, sizeof(ti_warp_rec))) != TI_OK) return st;
+    CK(cudaEventRecord(t.ev_d2h, s_dn));
+    T_inst += hc->n_inst; T_mem += hc->n_mem; T_txn += hc->n_txn; T_tb += hc->n_tb; T_warp += hc->n_warp;
+    ti_counters_add(&total, hc);
+  }
+  CK(cudaStreamSynchronize(s_dn));
+  CK(cudaStreamSynchronize(s_up));
+  CK(cudaStreamSynchronize(s_c));
+  if (overflow) {
+    // a capacity guess was too small for one shard: take the one-piece path, which re-decodes with exact sizes
+    if ((st = ti_kernel_upload(k, 0, k->body_len)) != TI_OK) return st;
+    if ((st = ti_kernel_decode(k)) != TI_OK) return st;
+    if ((st = ti_kernel_sync(k, NULL)) != TI_OK) return st;
+    return ti_kernel_fetch(k, v);
+  }
+  if (T_inst > 0x7ffffffeull || T_txn > 0xfffffffeull) { ti::set_error("more than 2^31 records in one kernel file"); return TI_ERR_TOO_LARGE; }
+  total.n_inst = T_inst; total.n_mem = T_mem; total.n_txn = T_txn; total.n_tb = T_tb; total.n_warp = T_warp;
+  total.text_bytes = k->body_len;
+  k->host_counters = total;
+  memset(&k->counts, 0, sizeof k->counts);
+  k->counts.n_inst = T_inst; k->counts.n_mem = T_mem; k->counts.n_txn = T_txn; k->counts.n_tb = T_tb; k->counts.n_warp = T_warp;
+  k->counts.text_bytes = k->body_len;
+  if (total.n_begin_tb != total.n_end_tb || total.n_begin_tb != T_tb || total.reserved[0] != T_warp) flags |= TI_EF_BAD_STRUCTURE;
+  k->counts.error_flags = flags;
+  k->counts.first_error_line_off = first_err == 0xffffffffu ? 0 : first_err;
+  k->sh_begin = 0; k->sh_len = k->body_len;
+  k->decode_ms = ms_sum;
+  k->synced = true; k->decoded = true; k->streamed = true;
+  if (flags) { ti::set_error("trace text outside the tracer grammar: flags 0x%x near body offset %u", flags, k->counts.first_error_line_off); return TI_ERR_PARSE; }
+  v->text = k->h_body;
+  v->inst = (const ti_inst_rec *)k->h_inst.p;
+  v->addr_rows = (const uint64_t *)k->h_rows.p;
+  v->txn_off = (const uint32_t *)k->h_txn_off.p;
+  v->txn = (const ti_txn_rec *)k->h_txn.p;
+  v->tb = (const ti_tb_rec *)k->h_tb.p;
+  v->warp = (const ti_warp_rec *)k->h_warp.p;
+  v->counts = k->counts;
   return TI_OK;
 }
 

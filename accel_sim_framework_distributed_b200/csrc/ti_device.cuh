@@ -124,6 +124,9 @@ struct DecodeParams {
   ti_txn_rec *txn;    uint64_t cap_txn;
   ti_tb_rec *tb;      uint64_t cap_tb;
   ti_warp_rec *warp;  uint64_t cap_warp;
+  // value offsets: what the preceding shards of the same kernel file produced, so that
+  // indices and text offsets stored in the records of a streamed shard are file-global
+  uint64_t off_inst, off_mem, off_txn, off_warp, off_text;
   // scratch
   State1 *state1;
   State2 *state2;

@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       unsigned kd;
       const unsigned o = inst_off[io];
       const unsigned le = line_end(nlmap32, o);
-      uint32_t fl = parse_inst_line(text, dlmap32, (int)o, le, P, tbase, r, kd);
+      uint32_t fl = parse_inst_line(text, dlmap32, (int)o, le, P, tbase + (uint32_t)P.off_text, r, kd);
       if (le - o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
       if (fl) { note_error(ms, fl, tbase + o); kd = 0; r.mem_idx = 0xFFFFFFFFu; r.pack_c &= 0x7f; }
       const uint4 *src = reinterpret_cast<const uint4 *>(&r);
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
           // instruction lines before this one = its rank in the sorted inst_off list
           uint32_t lo = 0, hi = n_inst;
           while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (inst_off[mid] < o) lo = mid + 1; else hi = mid; }
-          const uint64_t first_inst = base_inst + lo;
+          const uint64_t first_inst = base_inst + lo + P.off_inst;
           if (c == '#') {
             if (match_lit(text, q, "#BEGIN_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 1], 1u);
             else { q = o; if (match_lit(text, q, "#END_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 2], 1u); else fl = TI_EF_BAD_STRUCTURE; }
@@ -263,8 +263,8 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
             ti_tb_rec r;
             if (match_lit(text, q, "thread block = ") && parse_i32(text, q, r.x) && text[q++] == ',' &&
                 parse_i32(text, q, r.y) && text[q++] == ',' && parse_i32(text, q, r.z) && text[q] == '\n') {
-              r.text_off = cb - 16 + (uint64_t)o; r.line_len = (uint32_t)(q - o);
-              r.first_warp = (uint32_t)(base_warp + (ex >> 16)); r.first_inst = (uint32_t)first_inst;
+              r.text_off = cb - 16 + (uint64_t)o + P.off_text; r.line_len = (uint32_t)(q - o);
+              r.first_warp = (uint32_t)(base_warp + (ex >> 16) + P.off_warp); r.first_inst = (uint32_t)first_inst;
             } else { fl = TI_EF_BAD_STRUCTURE; r.text_off = cb - 16 + (uint64_t)o; r.x = r.y = r.z = 0; r.line_len = 0; r.first_warp = r.first_inst = 0; }
             const uint64_t at = base_tb + (ex & 0xffff);
             if (at < P.cap_tb) P.tb[at] = r;
@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       uint32_t slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
       if (slot + n_txn > (uint32_t)kTxnStage) slot = 0xFFFFu;
       txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
-      rp->mem_idx = (uint32_t)row;
+      rp->mem_idx = (uint32_t)(row + P.off_mem);
       if (n_txn && slot != 0xFFFFu) {
         const unsigned is_write = op == OP_STORE ? 1u : 0u;
         if (dense) dense_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       uint32_t slot = 0;
       if (lane == 0) {
         note_error(ms, fl, rp->opc_off);
-        rp->mem_idx = (uint32_t)row; rp->pack_c = (uint8_t)pack_c; rp->cycles = (uint8_t)cycles;
+        rp->mem_idx = (uint32_t)(row + P.off_mem); rp->pack_c = (uint8_t)pack_c; rp->cycles = (uint8_t)cycles;
         slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
         if (slot + n_txn > (uint32_t)kTxnStage) slot = 0xFFFFu;   // staging full: recomputed after look-back #2
         txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
@@ -409,14 +409,14 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       if (base_txn + n_txn_chunk > 0xfffffffeull) ov |= 32;
       if (ov) atomicOr(&P.g->overflow, ov);
       if (chunk == P.n_chunks - 1) {                   // last chunk: CSR sentinel + totals
-        if (base_mem + n_mem <= P.cap_mem) P.txn_off[base_mem + n_mem] = (uint32_t)(base_txn + n_txn_chunk);
+        if (base_mem + n_mem <= P.cap_mem) P.txn_off[base_mem + n_mem] = (uint32_t)(base_txn + n_txn_chunk + P.off_txn);
         P.counters[kCntNInst + 0] = base_inst + n_inst; P.counters[kCntNInst + 1] = base_mem + n_mem;
         P.counters[kCntNInst + 2] = base_txn + n_txn_chunk; P.counters[kCntNInst + 3] = base_tb + n_tb;
         P.counters[kCntNInst + 4] = base_warp + n_warp; P.counters[kCntNInst + 7] = P.len;
       }
     }
     for (uint32_t mo = tid; mo < n_mem; mo += kThreads)
-      if (base_mem + mo < P.cap_mem) P.txn_off[base_mem + mo] = (uint32_t)(base_txn + txn_loc[mo]);
+      if (base_mem + mo < P.cap_mem) P.txn_off[base_mem + mo] = (uint32_t)(base_txn + txn_loc[mo] + P.off_txn);
     // staged transactions -> HBM in file order: one thread moves one instruction's records
     // (32 instructions per warp in flight; a warp per instruction left 3/4 of the lanes idle)
     for (uint32_t mo = tid; mo < n_mem; mo += kThreads) {
@@ -485,11 +485,11 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
 // Framing check over the finished warp-header table (the reference would trip an
 // assert or index past a vector, trace_parser.cc:435-443): every "insts = n" must be
 // followed by exactly n instruction lines.
-__global__ void ti_check_kernel(const ti_warp_rec *warp, uint64_t cap_warp, const unsigned long long *counters, Globals *g) {
-  const uint64_t n_warp = counters[kCntNInst + 4], n_inst = counters[kCntNInst + 0];
+__global__ void ti_check_kernel(const ti_warp_rec *warp, uint64_t cap_warp, const unsigned long long *counters, Globals *g, uint64_t off_inst = 0) {
+  const uint64_t n_warp = counters[kCntNInst + 4], n_inst = counters[kCntNInst + 0] + off_inst;
   if (n_warp > cap_warp) return;  // the table overflowed: the host decodes again with exact capacities
   const uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (uint64_t)gridDim.x * blockDim.x;
-  if (t0 == 0 && (n_warp ? warp[0].first_inst != 0 : n_inst != 0)) atomicOr(&g->error_flags, (uint32_t)TI_EF_FRAMING);
+  if (t0 == 0 && (n_warp ? warp[0].first_inst != off_inst : n_inst != off_inst)) atomicOr(&g->error_flags, (uint32_t)TI_EF_FRAMING);
   for (uint64_t k = t0; k < n_warp; k += stride) {
     const uint64_t next = k + 1 < n_warp ? warp[k + 1].first_inst : n_inst;
     if (next - warp[k].first_inst != warp[k].n_insts) atomicOr(&g->error_flags, (uint32_t)TI_EF_FRAMING);

@@ -252,10 +252,7 @@ void trace_parser::get_next_threadblock_traces(std::vector<std::vector<inst_trac
   KernelState &s = it->second;
   if (!s.decoded) {
     // the whole kernel file in one fused launch; later calls only copy records out
-    ti_status st = ti_kernel_upload(s.k, 0, (size_t)-1);
-    if (st == TI_OK) st = ti_kernel_decode(s.k);
-    if (st == TI_OK) st = ti_kernel_sync(s.k, NULL);
-    if (st == TI_OK) st = ti_kernel_fetch(s.k, &s.view);
+    ti_status st = ti_kernel_decode_streamed(s.k, 0, &s.view);  // copies and kernel overlapped
     if (st != TI_OK) die("get_next_threadblock_traces", st);
     s.decoded = true;
   }

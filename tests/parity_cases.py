@@ -129,3 +129,25 @@ def run_sharded(tp, tmp_path, n_shards, **gen):
         if f not in ("reserved",):
             assert np.array_equal(acc[0][f], want["counters"][f]), f
     tp.kernel_finalizer(k)
+
+
+def run_streamed(tp, tmp_path, shard_bytes, **gen):
+    """The pipelined host -> host path returns exactly what the one-piece path returns."""
+    path = os.path.join(str(tmp_path), "kernel-1.traceg")
+    harness.generate(path, **gen)
+    k = tp.parse_kernel_info(path)
+    whole = k.run()
+    want = {n: getattr(whole, n).copy() for n in ("inst", "rows", "txn_off", "txn", "tb", "warp")}
+    wc = np.zeros(1, dtype=T.COUNTERS)
+    wc[0] = whole.counters
+    d = k.run_streamed(shard_bytes)
+    for n, w in want.items():
+        assert np.array_equal(getattr(d, n), w), n
+    for f in T.COUNTERS.names:
+        if f != "reserved":
+            assert np.array_equal(d.counters[f], wc[0][f]), f
+    # and a second time, reusing the pipeline's buffers
+    d = k.run_streamed(shard_bytes)
+    for n, w in want.items():
+        assert np.array_equal(getattr(d, n), w), n
+    tp.kernel_finalizer(k)

@@ -48,3 +48,7 @@ def test_emu_staging_overflow_and_capacity_retry(emu_parser, tmp_path):
     o = T.load_dump(harness.oracle_dump(path, str(tmp_path)))
     parity_cases.check_against_dump(d, o, offsets=harness.oracle_kind() == "port")
     emu_parser.kernel_finalizer(k)
+
+
+def test_emu_streamed(emu_parser, tmp_path):
+    parity_cases.run_streamed(emu_parser, tmp_path, 40000, profile=5, seed=21, n_tb=24, insts_per_warp=8, block_threads=96)

@@ -117,3 +117,8 @@ def test_full_size_properties(cuda_parser):
     d2 = k.run()
     assert np.array_equal(inst1, d2.inst) and np.array_equal(txn1, d2.txn)
     cuda_parser.kernel_finalizer(k)
+
+
+@pytest.mark.parametrize("shard_bytes", [1 << 20, 300000])
+def test_streamed_host_path(cuda_parser, tmp_path, shard_bytes):
+    parity_cases.run_streamed(cuda_parser, tmp_path, shard_bytes, profile=5, seed=31, n_tb=800, insts_per_warp=10, block_threads=128)
