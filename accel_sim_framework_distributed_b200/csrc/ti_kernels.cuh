@@ -188,6 +188,10 @@ TI_D void cta_lookback1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64
     st_vol64(&st[c].agg, kValid | (unsigned long long)agg[3] << 42 | (unsigned long long)agg[2] << 28 |
                              (unsigned long long)agg[1] << 14 | agg[0]);
   excl[0] = excl[1] = excl[2] = excl[3] = 0;
+#ifdef TI_EXP_NOWAIT  // tuning experiment only (wrong output): what the kernel costs with no look-back at all
+  excl[0] = (uint64_t)c * 300; excl[1] = (uint64_t)c * 120; excl[2] = c; excl[3] = (uint64_t)c * 12;
+  return;
+#endif
   for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= kThreads) {
     const int64_t j = idx - (int64_t)threadIdx.x;
     unsigned long long A = kValid, I0 = kValid, I1 = kValid;
@@ -230,6 +234,9 @@ TI_D uint64_t cta_lookback2(State2 *st, uint32_t c, uint32_t agg, LbWarp *lb) {
   const unsigned lane = lane_id(), w = threadIdx.x >> 5;
   if (threadIdx.x == 0 && c) st_vol64(&st[c].w, kAggValid | agg);
   uint64_t excl = 0;
+#ifdef TI_EXP_NOWAIT
+  return (uint64_t)c * 470;
+#endif
   for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= kThreads) {
     const int64_t j = idx - (int64_t)threadIdx.x;
     unsigned long long W = kValid;
