@@ -224,12 +224,116 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     const uint32_t n_mem = p3 & 0xffff, n_fast = p3 >> 16, n_slow = n_mem - n_fast;
 
     TI_STAMP(4);   // P3
-    // ---------------------------------------------------------------- P4 look-back #1
-    uint64_t ex1[4];
+    // ---------------------------------------------------------------- P4 look-back #1: publish now, resolve late
+    // Everything up to P6a works with chunk-relative positions so that the prefix is needed only
+    // afterwards: thread-block / warp headers are parked in the tail of the transaction staging
+    // area, base+stride descriptors in the (by then dead) line-offset lists.  A chunk with more
+    // headers than the parking area holds (no tracer writes one) resolves first and writes direct.
+    const uint32_t agg1[4] = {n_inst, n_mem, n_tb, n_warp};
+    cta_publish1(P.state1, chunk, agg1);
+    const uint32_t park_slots = n_tb + ((n_warp + 1) >> 1);
+    const bool late = park_slots <= (uint32_t)kParkMax;
+    const uint32_t stage_cap = late ? (uint32_t)kTxnStage - park_slots : (uint32_t)kTxnStage;
+    ti_tb_rec *park_tb = reinterpret_cast<ti_tb_rec *>(stage + stage_cap);
+    ti_warp_rec *park_warp = reinterpret_cast<ti_warp_rec *>(stage + stage_cap + n_tb);
+    uint64_t ex1[4] = {0, 0, 0, 0};
+    if (!late) cta_resolve1(P.state1, chunk, agg1, ex1, ms->lb);
+
+    TI_STAMP(5);   // P4 publish (+ early resolve)
+    // ---------------------------------------------------------------- P5 structural lines
+    // ordinals of "thread block" (low half) and "warp" (high half) lines among the structural lines
     {
-      const uint32_t agg[4] = {n_inst, n_mem, n_tb, n_warp};
-      cta_lookback1(P.state1, chunk, agg, ex1, ms->lb);
+      ti_tb_rec *tb_out = late ? park_tb : P.tb + ex1[2];
+      ti_warp_rec *warp_out = late ? park_warp : P.warp + ex1[3];
+      const uint64_t tb_room = late ? ~0ull : (P.cap_tb > ex1[2] ? P.cap_tb - ex1[2] : 0);
+      const uint64_t warp_room = late ? ~0ull : (P.cap_warp > ex1[3] ? P.cap_warp - ex1[3] : 0);
+      const uint64_t inst0 = late ? 0 : ex1[0] + P.off_inst, warp0 = late ? 0 : ex1[3] + P.off_warp;
+      block_scan(
+          n_sl, ms->warp_tot,
+          [&](uint32_t i) { const unsigned c = text[sl_off[i]]; return (uint32_t)(c == 't' ? 1u : c == 'w' ? 0x10000u : 0u); },
+          [&](uint32_t i, uint32_t ex, uint32_t) {
+            const int o = sl_off[i];
+            int q = o;
+            const unsigned c = text[o];
+            uint32_t fl = 0;
+            // instruction lines before this one = its rank in the sorted inst_off list
+            uint32_t lo = 0, hi = n_inst;
+            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (inst_off[mid] < o) lo = mid + 1; else hi = mid; }
+            const uint64_t first_inst = inst0 + lo;
+            if (c == '#') {
+              if (match_lit(text, q, "#BEGIN_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 1], 1u);
+              else { q = o; if (match_lit(text, q, "#END_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 2], 1u); else fl = TI_EF_BAD_STRUCTURE; }
+            } else if (c == 't') {                        // trace_parser.cc:423-427
+              ti_tb_rec r;
+              if (match_lit(text, q, "thread block = ") && parse_i32(text, q, r.x) && text[q++] == ',' &&
+                  parse_i32(text, q, r.y) && text[q++] == ',' && parse_i32(text, q, r.z) && text[q] == '\n') {
+                r.text_off = cb - 16 + (uint64_t)o + P.off_text; r.line_len = (uint32_t)(q - o);
+                r.first_warp = (uint32_t)(warp0 + (ex >> 16)); r.first_inst = (uint32_t)first_inst;
+              } else { fl = TI_EF_BAD_STRUCTURE; r.text_off = cb - 16 + (uint64_t)o; r.x = r.y = r.z = 0; r.line_len = 0; r.first_warp = r.first_inst = 0; }
+              if ((ex & 0xffff) < tb_room) tb_out[ex & 0xffff] = r;
+            } else if (c == 'w') {                        // trace_parser.cc:428-437
+              int32_t w = 0, n = 0;
+              bool ok = match_lit(text, q, "warp = ") && parse_i32(text, q, w) && text[q] == '\n' && w >= 0;
+              if (ok) {  // the next non-blank line must be "insts = n"
+                while (text[q] == '\n' && q < 16 + kChunk + kSlack) ++q;
+                ok = match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0;
+              }
+              if (!ok) { fl = TI_EF_BAD_STRUCTURE; w = n = 0; }
+              ti_warp_rec r;  // written even when malformed so the table never holds uninitialised rows
+              r.warp_id = (uint32_t)w; r.n_insts = (uint32_t)n; r.first_inst = (uint32_t)first_inst; r.reserved = 0;
+              if ((ex >> 16) < warp_room) warp_out[ex >> 16] = r;
+            } else if (c == 'i') {
+              int32_t n = 0;
+              if (match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0) atomicAdd(&cnt[kCntConst + 4], 1u);
+              else fl = TI_EF_BAD_STRUCTURE;
+            } else fl = TI_EF_BAD_STRUCTURE;
+            if (line_end(nlmap32, (unsigned)o) - (unsigned)o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
+            note_error(ms, fl, tbase + (uint32_t)o);
+          });
     }
+
+    TI_STAMP(6);   // P5
+    // ---------------------------------------------------------------- P6a base+stride: thread per instruction
+    // Coalesces into the staging area; the address row and the final mem_idx need the prefix and
+    // are written in P6c from the descriptor parked here.  The line-offset lists are dead now
+    // (P5 has ended with a barrier) and hold the descriptors.
+    StrideNote *notes = reinterpret_cast<StrideNote *>(smem + oInstOff);
+    for (uint32_t fo = tid; fo < n_fast; fo += kThreads) {
+      const uint32_t mo = fast_list[fo];
+      ti_inst_rec *rp = recs + mem_list[mo];
+      const uint32_t mask = rp->mask, tmp = rp->mem_idx;
+      const unsigned ds = rp->data_size, op = rp->op;
+      StrideDesc d;
+      uint32_t fl = 0;
+      if (fo >= (uint32_t)kNoteCap || !stride_parse(text, tmp & 0xffff, mask, ds ? ds : 1, d, fl)) {
+        // no room for a descriptor, or the progression wraps around 2^64 (not monotone): warp path
+        slow_list[n_slow + atomicAdd(&ms->n_extra, 1u)] = (uint16_t)mo;
+        if (fo < (uint32_t)kNoteCap) notes[fo].flags = kNoteSkip;
+        continue;
+      }
+      const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
+      if (!fl && mask && !seg) fl = TI_EF_BAD_WIDTH;
+      if (fl) { note_error(ms, fl, rp->opc_off); if (fl & TI_EF_BAD_NUMBER) d.n = 0; }
+      StrideNote nt;
+      nt.base = d.base; nt.stride = (int32_t)d.stride; nt.flags = d.n ? 0u : kNoteEmpty;
+      notes[fo] = nt;
+      const bool dense = !fl && mask && stride_is_dense(d, ds);
+      const unsigned n_txn = (fl || !mask) ? 0u : dense ? dense_count(d, ds, seg) : stride_count(d, ds, seg);
+      uint32_t slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
+      if (slot + n_txn > stage_cap) slot = 0xFFFFu;
+      txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
+      if (n_txn && slot != 0xFFFFu) {
+        const unsigned is_write = op == OP_STORE ? 1u : 0u;
+        if (dense) dense_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
+        else stride_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
+      }
+    }
+    __syncthreads();
+    const uint32_t n_warp_path = n_slow + ms->n_extra;
+
+    TI_STAMP(7);   // P6a
+    // ---------------------------------------------------------------- P4' resolve look-back #1
+    if (late) cta_resolve1(P.state1, chunk, agg1, ex1, ms->lb);
     const uint64_t base_inst = ex1[0], base_mem = ex1[1], base_tb = ex1[2], base_warp = ex1[3];
     if (tid == 0) {
       uint32_t ov = 0;
@@ -241,92 +345,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       if (ov) atomicOr(&P.g->overflow, ov);
     }
 
-    TI_STAMP(5);   // P4
-    // ---------------------------------------------------------------- P5 structural lines
-    // ordinals of "thread block" (low half) and "warp" (high half) lines among the structural lines
-    block_scan(
-        n_sl, ms->warp_tot,
-        [&](uint32_t i) { const unsigned c = text[sl_off[i]]; return (uint32_t)(c == 't' ? 1u : c == 'w' ? 0x10000u : 0u); },
-        [&](uint32_t i, uint32_t ex, uint32_t) {
-          const int o = sl_off[i];
-          int q = o;
-          const unsigned c = text[o];
-          uint32_t fl = 0;
-          // instruction lines before this one = its rank in the sorted inst_off list
-          uint32_t lo = 0, hi = n_inst;
-          while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (inst_off[mid] < o) lo = mid + 1; else hi = mid; }
-          const uint64_t first_inst = base_inst + lo + P.off_inst;
-          if (c == '#') {
-            if (match_lit(text, q, "#BEGIN_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 1], 1u);
-            else { q = o; if (match_lit(text, q, "#END_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 2], 1u); else fl = TI_EF_BAD_STRUCTURE; }
-          } else if (c == 't') {                        // trace_parser.cc:423-427
-            ti_tb_rec r;
-            if (match_lit(text, q, "thread block = ") && parse_i32(text, q, r.x) && text[q++] == ',' &&
-                parse_i32(text, q, r.y) && text[q++] == ',' && parse_i32(text, q, r.z) && text[q] == '\n') {
-              r.text_off = cb - 16 + (uint64_t)o + P.off_text; r.line_len = (uint32_t)(q - o);
-              r.first_warp = (uint32_t)(base_warp + (ex >> 16) + P.off_warp); r.first_inst = (uint32_t)first_inst;
-            } else { fl = TI_EF_BAD_STRUCTURE; r.text_off = cb - 16 + (uint64_t)o; r.x = r.y = r.z = 0; r.line_len = 0; r.first_warp = r.first_inst = 0; }
-            const uint64_t at = base_tb + (ex & 0xffff);
-            if (at < P.cap_tb) P.tb[at] = r;
-          } else if (c == 'w') {                        // trace_parser.cc:428-437
-            int32_t w = 0, n = 0;
-            bool ok = match_lit(text, q, "warp = ") && parse_i32(text, q, w) && text[q] == '\n' && w >= 0;
-            if (ok) {  // the next non-blank line must be "insts = n"
-              while (text[q] == '\n' && q < 16 + kChunk + kSlack) ++q;
-              ok = match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0;
-            }
-            if (!ok) { fl = TI_EF_BAD_STRUCTURE; w = n = 0; }
-            ti_warp_rec r;  // written even when malformed so the table never holds uninitialised rows
-            r.warp_id = (uint32_t)w; r.n_insts = (uint32_t)n; r.first_inst = (uint32_t)first_inst; r.reserved = 0;
-            const uint64_t at = base_warp + (ex >> 16);
-            if (at < P.cap_warp) P.warp[at] = r;
-          } else if (c == 'i') {
-            int32_t n = 0;
-            if (match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0) atomicAdd(&cnt[kCntConst + 4], 1u);
-            else fl = TI_EF_BAD_STRUCTURE;
-          } else fl = TI_EF_BAD_STRUCTURE;
-          if (line_end(nlmap32, (unsigned)o) - (unsigned)o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
-          note_error(ms, fl, tbase + (uint32_t)o);
-        });
-
-    TI_STAMP(6);   // P5
-    // ---------------------------------------------------------------- P6a base+stride: thread per instruction
-    for (uint32_t fo = tid; fo < n_fast; fo += kThreads) {
-      const uint32_t mo = fast_list[fo];
-      ti_inst_rec *rp = recs + mem_list[mo];
-      const uint32_t mask = rp->mask, tmp = rp->mem_idx;
-      const unsigned ds = rp->data_size, op = rp->op;
-      StrideDesc d;
-      uint32_t fl = 0;
-      if (!stride_parse(text, tmp & 0xffff, mask, ds ? ds : 1, d, fl)) {
-        slow_list[n_slow + atomicAdd(&ms->n_extra, 1u)] = (uint16_t)mo;  // wraps around 2^64: not monotone
-        continue;
-      }
-      const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
-      if (!fl && mask && !seg) fl = TI_EF_BAD_WIDTH;
-      if (fl) { note_error(ms, fl, rp->opc_off); if (fl & TI_EF_BAD_NUMBER) d.n = 0; }
-      const uint64_t row = base_mem + mo;
-      if (row < P.cap_mem) {
-        ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(P.rows + row * 32);
-#pragma unroll 4
-        for (unsigned l = 0; l < 32; l += 2) dst[l >> 1] = make_ulonglong2(stride_addr(d, l), stride_addr(d, l + 1));
-      }
-      const bool dense = !fl && mask && stride_is_dense(d, ds);
-      const unsigned n_txn = (fl || !mask) ? 0u : dense ? dense_count(d, ds, seg) : stride_count(d, ds, seg);
-      uint32_t slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
-      if (slot + n_txn > (uint32_t)kTxnStage) slot = 0xFFFFu;
-      txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
-      rp->mem_idx = (uint32_t)(row + P.off_mem);
-      if (n_txn && slot != 0xFFFFu) {
-        const unsigned is_write = op == OP_STORE ? 1u : 0u;
-        if (dense) dense_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
-        else stride_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
-      }
-    }
-    __syncthreads();
-    const uint32_t n_warp_path = n_slow + ms->n_extra;
-
-    TI_STAMP(7);   // P6a
+    TI_STAMP(8);   // P4' resolve
     // ---------------------------------------------------------------- P6b everything else: warp per instruction
     for (;;) {
       uint32_t so = 0;
@@ -374,7 +393,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         note_error(ms, fl, rp->opc_off);
         rp->mem_idx = (uint32_t)(row + P.off_mem); rp->pack_c = (uint8_t)pack_c; rp->cycles = (uint8_t)cycles;
         slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
-        if (slot + n_txn > (uint32_t)kTxnStage) slot = 0xFFFFu;   // staging full: recomputed after look-back #2
+        if (slot + n_txn > stage_cap) slot = 0xFFFFu;             // staging full: recomputed after look-back #2
         txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
       }
       slot = __shfl_sync(kFull, slot, 0);
@@ -386,9 +405,9 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
     __syncthreads();
 
-    TI_STAMP(8);   // P6b
+    TI_STAMP(9);   // P6b
     // Take the next ticket only now and prefetch that chunk's text into the other buffer (free
-    // since the top-of-loop barrier) while P7/P8 run.  Taking it any earlier would hand out
+    // since the top-of-loop barrier) while the rest runs.  Taking it any earlier would hand out
     // tickets a whole chunk time before the work starts, so a chunk's predecessor could begin
     // later than the chunk itself and the look-back would wait for it.
     if (tid == 0) {
@@ -396,12 +415,81 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       ms->chunk_next = nxt;
       if (TI_TEXT_BUFS == 2 && nxt < P.n_chunks) issue_bulk(nxt, buf ^ 1);
     }
-    // ---------------------------------------------------------------- P7 look-back #2 + ordered copy-out
+    // ---------------------------------------------------------------- P7 look-back #2: publish now, resolve late
     const uint32_t n_txn_chunk = block_scan(
         n_mem, ms->warp_tot, [&](uint32_t i) { return (uint32_t)txn_cnt[i]; },
         [&](uint32_t i, uint32_t ex, uint32_t) { txn_loc[i] = (uint16_t)ex; });
-    const uint64_t base_txn = cta_lookback2(P.state2, chunk, n_txn_chunk, ms->lb);
-    TI_STAMP(9);   // P7 scan + look-back #2
+    cta_publish2(P.state2, chunk, n_txn_chunk);
+
+    TI_STAMP(10);  // P7 scan + publish
+    // ---------------------------------------------------------------- P6c parked headers and address rows out
+    if (late) {
+      for (uint32_t i = tid; i < n_tb; i += kThreads) {
+        ti_tb_rec r = park_tb[i];
+        if (r.line_len) { r.first_warp += (uint32_t)(base_warp + P.off_warp); r.first_inst += (uint32_t)(base_inst + P.off_inst); }
+        if (base_tb + i < P.cap_tb) P.tb[base_tb + i] = r;
+      }
+      for (uint32_t i = tid; i < n_warp; i += kThreads) {
+        ti_warp_rec r = park_warp[i];
+        r.first_inst += (uint32_t)(base_inst + P.off_inst);
+        if (base_warp + i < P.cap_warp) P.warp[base_warp + i] = r;
+      }
+    }
+    {
+      const uint32_t n_notes = n_fast < (uint32_t)kNoteCap ? n_fast : (uint32_t)kNoteCap;
+      for (uint32_t fo = tid; fo < n_notes; fo += kThreads) {
+        const StrideNote nt = notes[fo];
+        if (nt.flags & kNoteSkip) continue;             // went to the warp path, which wrote its row
+        const uint32_t mo = fast_list[fo];
+        ti_inst_rec *rp = recs + mem_list[mo];
+        const uint32_t mask = rp->mask;
+        StrideDesc d;
+        d.base = nt.base; d.stride = nt.stride; d.first = 0; d.n = 0;
+        if (mask && !(nt.flags & kNoteEmpty)) {
+          d.first = __ffs(mask) - 1;
+          const uint32_t inv = ~(mask >> d.first);
+          d.n = inv ? __ffs(inv) - 1 : 32;
+        }
+        const uint64_t row = base_mem + mo;
+        if (row < P.cap_mem) {
+          ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(P.rows + row * 32);
+#pragma unroll 4
+          for (unsigned l = 0; l < 32; l += 2) dst[l >> 1] = make_ulonglong2(stride_addr(d, l), stride_addr(d, l + 1));
+        }
+        rp->mem_idx = (uint32_t)(row + P.off_mem);
+      }
+    }
+    __syncthreads();   // mem_idx of every record is final
+
+    TI_STAMP(11);  // P6c
+    // ---------------------------------------------------------------- P8 records out + counters
+    {
+      const uint4 *src = reinterpret_cast<const uint4 *>(recs);
+      uint4 *dst = reinterpret_cast<uint4 *>(P.inst + base_inst);
+      for (uint32_t k = tid; k < 2 * n_inst; k += kThreads)
+        if (base_inst + (k >> 1) < P.cap_inst) dst[k] = src[k];
+    }
+    for (uint32_t io = tid; io < n_inst; io += kThreads) {
+      const ti_inst_rec *rp = recs + io;
+      const unsigned op = rp->op, sp = rp->pack_a & 0x1f, act = __popc(rp->mask);
+      atomicAdd(&cnt[kCntHist + sp * 33 + act], 1u);
+      atomicAdd(&cnt[kCntOp + fold_op(op)], 1u);
+      if (op == OP_LOAD || op == OP_STORE || op == OP_MEMBAR || op == OP_TLOAD || op == OP_TSTORE) {
+        const unsigned st = (op == OP_STORE || op == OP_TSTORE || (rp->pack_b >> 4 & 3) == 2) ? 1u : 0u;
+        if (act) atomicAdd(&cnt[kCntSpace + (rp->pack_c & 0xf) * 2 + st], act);
+      }
+      if (rp->pack_b >> 7) atomicAdd(&cnt[kCntConst], 1u);
+      if (rp->cycles) atomicAdd(&cnt[kCntConst + 3], (uint32_t)rp->cycles);
+    }
+    if (tid == 0 && ms->err) {
+      atomicOr(&P.g->error_flags, ms->err);
+      atomicMin(&P.g->first_error_off, ms->first_err);
+    }
+
+    TI_STAMP(12);  // P8
+    // ---------------------------------------------------------------- P7' resolve look-back #2 + ordered copy-out
+    const uint64_t base_txn = cta_resolve2(P.state2, chunk, n_txn_chunk, ms->lb);
+    TI_STAMP(13);  // P7' resolve
     if (TI_TEXT_BUFS == 2 && ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, buf ^ 1);   // visible after the barriers above
     if (tid == 0) {
       uint32_t ov = 0;
@@ -428,10 +516,10 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       for (uint32_t k = 0; k < n; ++k)
         if (at + k < P.cap_txn) { dst[2 * k] = src[2 * k]; dst[2 * k + 1] = src[2 * k + 1]; }
     }
-    if (ms->stage_used > (uint32_t)kTxnStage) {      // warp-uniform: some instructions did not fit the staging area
+    if (ms->stage_used > stage_cap) {                // warp-uniform: some instructions did not fit the staging area
       for (uint32_t mo = wid; mo < n_mem; mo += kWarps) {
         if (txn_slot[mo] != 0xFFFFu || !txn_cnt[mo]) continue;
-        // coalesce again from the row written in P6
+        // coalesce again from the row written in P6b / P6c
         const uint64_t at = base_txn + txn_loc[mo];
         const ti_inst_rec *rp = recs + mem_list[mo];
         const uint64_t row = base_mem + mo;
@@ -450,32 +538,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         if (pos[1] < m && at + pos[1] < P.cap_txn) P.txn[at + pos[1]] = reduce_and_send(t2[1], seg, type, is_write);
       }
     }
-
-    TI_STAMP(10);  // P7 copy-out
-    // ---------------------------------------------------------------- P8 records out + counters
-    {
-      const uint4 *src = reinterpret_cast<const uint4 *>(recs);
-      uint4 *dst = reinterpret_cast<uint4 *>(P.inst + base_inst);
-      for (uint32_t k = tid; k < 2 * n_inst; k += kThreads)
-        if (base_inst + (k >> 1) < P.cap_inst) dst[k] = src[k];
-    }
-    for (uint32_t io = tid; io < n_inst; io += kThreads) {
-      const ti_inst_rec *rp = recs + io;
-      const unsigned op = rp->op, sp = rp->pack_a & 0x1f, act = __popc(rp->mask);
-      atomicAdd(&cnt[kCntHist + sp * 33 + act], 1u);
-      atomicAdd(&cnt[kCntOp + fold_op(op)], 1u);
-      if (op == OP_LOAD || op == OP_STORE || op == OP_MEMBAR || op == OP_TLOAD || op == OP_TSTORE) {
-        const unsigned st = (op == OP_STORE || op == OP_TSTORE || (rp->pack_b >> 4 & 3) == 2) ? 1u : 0u;
-        if (act) atomicAdd(&cnt[kCntSpace + (rp->pack_c & 0xf) * 2 + st], act);
-      }
-      if (rp->pack_b >> 7) atomicAdd(&cnt[kCntConst], 1u);
-      if (rp->cycles) atomicAdd(&cnt[kCntConst + 3], (uint32_t)rp->cycles);
-    }
-    if (tid == 0 && ms->err) {
-      atomicOr(&P.g->error_flags, ms->err);
-      atomicMin(&P.g->first_error_off, ms->first_err);
-    }
-    TI_STAMP(11);  // P8
+    TI_STAMP(14);  // P7' copy-out
     if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }
   }
   __syncthreads();

@@ -63,6 +63,14 @@ constexpr int oMisc = oDlMap + align16(kTextBytes / 16 * 2 + 4);
 constexpr int kSmemBytes = oMisc + align16((int)sizeof(Misc));
 static_assert(kTextBytes % 16 == 0 && kChunk % 16 == 0 && kThreads % 32 == 0, "chunk geometry");
 static_assert(kTextBytes < 65536, "smem offsets are 16 bit");
+// Chunk-relative results parked until look-back #1 resolves (see P4 in ti_kernel_main.cuh):
+// thread-block / warp headers in the last slots of the staging area, base+stride descriptors
+// over the line-offset lists.
+constexpr int kParkMax = 128;                                // staging slots (32 B) lent to parked headers
+struct StrideNote { uint64_t base; int32_t stride; uint32_t flags; };
+constexpr uint32_t kNoteSkip = 1, kNoteEmpty = 2;            // handled by the warp path / no lane carries an address
+constexpr int kNoteCap = (oMemList - oInstOff) / (int)sizeof(StrideNote);
+static_assert(kParkMax < kTxnStage && oInstOff % 16 == 0 && sizeof(StrideNote) == 16, "parking areas");
 constexpr int kVecPerWarp = ((kChunk / 16 + kWarps - 1) / kWarps + 31) & ~31;  // 16 B vectors of the chunk per warp
 constexpr int kVecIters = kVecPerWarp / 32;
 
@@ -182,11 +190,17 @@ TI_D uint64_t lookback2(State2 *st, uint32_t c, uint32_t agg) {
 // typically ~100 chunks back.  A single warp needed several dependent 32-wide rounds of L2
 // round trips for that (measured: 20% of the kernel); the whole CTA needs one.
 
-TI_D void cta_lookback1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64_t (&excl)[4], LbWarp *lb) {
-  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
+// Publish and resolve are separate calls: a chunk resolves only once EVERY chunk before it has
+// published, i.e. at the running maximum of ~300 in-flight predecessors' publish times, so
+// whatever work does not need the prefix is placed between the two calls to absorb that jitter.
+TI_D void cta_publish1(State1 *st, uint32_t c, const uint32_t (&agg)[4]) {
   if (threadIdx.x == 0)
     st_vol64(&st[c].agg, kValid | (unsigned long long)agg[3] << 42 | (unsigned long long)agg[2] << 28 |
                              (unsigned long long)agg[1] << 14 | agg[0]);
+}
+
+TI_D void cta_resolve1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64_t (&excl)[4], LbWarp *lb) {
+  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
   excl[0] = excl[1] = excl[2] = excl[3] = 0;
 #ifdef TI_EXP_NOWAIT  // tuning experiment only (wrong output): what the kernel costs with no look-back at all
   excl[0] = (uint64_t)c * 300; excl[1] = (uint64_t)c * 120; excl[2] = c; excl[3] = (uint64_t)c * 12;
@@ -230,9 +244,12 @@ TI_D void cta_lookback1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64
   }
 }
 
-TI_D uint64_t cta_lookback2(State2 *st, uint32_t c, uint32_t agg, LbWarp *lb) {
-  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
+TI_D void cta_publish2(State2 *st, uint32_t c, uint32_t agg) {
   if (threadIdx.x == 0 && c) st_vol64(&st[c].w, kAggValid | agg);
+}
+
+TI_D uint64_t cta_resolve2(State2 *st, uint32_t c, uint32_t agg, LbWarp *lb) {
+  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
   uint64_t excl = 0;
 #ifdef TI_EXP_NOWAIT
   return (uint64_t)c * 470;

@@ -134,6 +134,11 @@ VALID = {
     "edge_fermi_segments": (image([(0, 0, 0, [W0])]), dict(coalesce_arch=20)),
     "edge_subwarps_broadcast": (image([(0, 0, 0, [W0])]), dict(mem_warp_parts=4, shmem_limited_broadcast=1, num_shmem_bank=16, clock_gated_lanes=0)),
     "edge_empty_kernel": (image([]), {}),
+    # header-dense: ~150 thread blocks per 16 KiB chunk, more than the kernel's header parking area
+    # holds, across several chunks; a base+stride instruction every 7th block keeps rows in play
+    "edge_many_headers": (image([(i % 50, i // 50, 0, [["0000 ffffffff 1 R1 FADD 2 R2 R3 0 0"] if i % 3 else [],
+                                                       ["0010 ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x7f00000%05x 4 0" % (i * 128)] if i % 7 == 0 else []])
+                                 for i in range(700)]), {}),
     "edge_ampere": (image([(0, 0, 0, [[l for l in W0 if "MEMBAR" not in l] + ["0350 ffffffff 1 R2 LDSM.16.M88.4 1 R4 2 1 0x400 16 0"]])], bv=86), {}),
 }
 
