@@ -93,6 +93,62 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
   };
 
+  // ---- transactions of one chunk out, in file order: resolve look-back #2, CSR offsets, staged
+  // records -> HBM.  Runs either at the end of the chunk's own iteration (staging overflowed:
+  // `recompute` coalesces the spilled instructions again from their address rows, which needs the
+  // chunk's records) or, normally, in the NEXT iteration just before the staging area is reused.
+  auto finish_txn = [&](uint32_t c, uint32_t n_mem, uint32_t n_txn_chunk, uint64_t base_mem, bool recompute) {
+    const uint64_t base_txn = cta_resolve2(P.state2, c, n_txn_chunk, ms->lb);
+    if (tid == 0) {
+      uint32_t ov = 0;
+      if (base_txn + n_txn_chunk > P.cap_txn) ov |= 4;
+      if (base_txn + n_txn_chunk > 0xfffffffeull) ov |= 32;
+      if (ov) atomicOr(&P.g->overflow, ov);
+      if (c == P.n_chunks - 1) {                       // last chunk: CSR sentinel + total
+        if (base_mem + n_mem <= P.cap_mem) P.txn_off[base_mem + n_mem] = (uint32_t)(base_txn + n_txn_chunk + P.off_txn);
+        P.counters[kCntNInst + 2] = base_txn + n_txn_chunk;
+      }
+    }
+    for (uint32_t mo = tid; mo < n_mem; mo += kThreads)
+      if (base_mem + mo < P.cap_mem) P.txn_off[base_mem + mo] = (uint32_t)(base_txn + txn_loc[mo] + P.off_txn);
+    // one thread moves one instruction's records (32 instructions per warp in flight; a warp per
+    // instruction left 3/4 of the lanes idle)
+    for (uint32_t mo = tid; mo < n_mem; mo += kThreads) {
+      const uint32_t n = txn_cnt[mo], slot = txn_slot[mo];
+      if (!n || slot == 0xFFFFu) continue;
+      const uint64_t at = base_txn + txn_loc[mo];
+      const uint4 *src = reinterpret_cast<const uint4 *>(stage + slot);
+      uint4 *dst = reinterpret_cast<uint4 *>(P.txn + at);
+      for (uint32_t k = 0; k < n; ++k)
+        if (at + k < P.cap_txn) { dst[2 * k] = src[2 * k]; dst[2 * k + 1] = src[2 * k + 1]; }
+    }
+    if (recompute) {                                 // CTA-uniform
+      for (uint32_t mo = wid; mo < n_mem; mo += kWarps) {
+        if (txn_slot[mo] != 0xFFFFu || !txn_cnt[mo]) continue;
+        const uint64_t at = base_txn + txn_loc[mo];
+        const ti_inst_rec *rp = recs + mem_list[mo];
+        const uint64_t row = base_mem + mo;
+        const uint64_t addr = row < P.cap_mem ? __ldcg(P.rows + row * 32 + lane) : 0;   // written in P6b / P6c
+        const unsigned ds = rp->data_size, pack_b = rp->pack_b, op = rp->op;
+        const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
+        const unsigned is_write = (op == OP_STORE || op == OP_TSTORE || (pack_b >> 4 & 3) == 2) ? 1u : 0u;
+        Txn t2[2];
+        unsigned pos[2] = {~0u, ~0u};
+        uint32_t fl = 0;
+        unsigned m;
+        if (pack_b >> 6 & 1) m = coalesce_atomic(P, rp->mask, addr, ds, seg, t2[0], pos[0], fl);
+        else m = coalesce_global(P, rp->mask, addr, ds, seg, t2, pos, wscratch);
+        const unsigned type = is_write ? 4u : 0u;
+        if (pos[0] < m && at + pos[0] < P.cap_txn) P.txn[at + pos[0]] = reduce_and_send(t2[0], seg, type, is_write);
+        if (pos[1] < m && at + pos[1] < P.cap_txn) P.txn[at + pos[1]] = reduce_and_send(t2[1], seg, type, is_write);
+      }
+    }
+    __syncthreads();   // the staging area and the txn_* lists may be reused
+  };
+  bool pend = false;   // a chunk whose transactions are still parked in shared memory (CTA-uniform)
+  uint32_t pend_chunk = 0, pend_n_mem = 0, pend_n_txn = 0, pend_stage_used = 0;
+  uint64_t pend_base_mem = 0;
+
   // prologue: first ticket, first bulk copy
   if (tid == 0) {
     mbar_init(&ms->mbar[0], 1);
@@ -238,6 +294,10 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     ti_warp_rec *park_warp = reinterpret_cast<ti_warp_rec *>(stage + stage_cap + n_tb);
     uint64_t ex1[4] = {0, 0, 0, 0};
     if (!late) cta_resolve1(P.state1, chunk, agg1, ex1, ms->lb);
+    if (pend && late && pend_stage_used > stage_cap) {   // the previous chunk's staged records reach into this chunk's parking area
+      finish_txn(pend_chunk, pend_n_mem, pend_n_txn, pend_base_mem, false);
+      pend = false;
+    }
 
     TI_STAMP(5);   // P4 publish (+ early resolve)
     // ---------------------------------------------------------------- P5 structural lines
@@ -293,6 +353,11 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
 
     TI_STAMP(6);   // P5
+    if (pend) {        // the previous chunk's transactions, before P6a reuses the staging area
+      finish_txn(pend_chunk, pend_n_mem, pend_n_txn, pend_base_mem, false);
+      pend = false;
+    }
+    TI_STAMP(14);  // P7' previous chunk: resolve look-back #2 + copy-out
     // ---------------------------------------------------------------- P6a base+stride: thread per instruction
     // Coalesces into the staging area; the address row and the final mem_idx need the prefix and
     // are written in P6c from the descriptor parked here.  The line-offset lists are dead now
@@ -406,20 +471,25 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     __syncthreads();
 
     TI_STAMP(9);   // P6b
-    // Take the next ticket only now and prefetch that chunk's text into the other buffer (free
-    // since the top-of-loop barrier) while the rest runs.  Taking it any earlier would hand out
-    // tickets a whole chunk time before the work starts, so a chunk's predecessor could begin
-    // later than the chunk itself and the look-back would wait for it.
-    if (tid == 0) {
-      const uint32_t nxt = atomicAdd(&P.g->ticket, 1u);
-      ms->chunk_next = nxt;
-      if (TI_TEXT_BUFS == 2 && nxt < P.n_chunks) issue_bulk(nxt, buf ^ 1);
-    }
-    // ---------------------------------------------------------------- P7 look-back #2: publish now, resolve late
+    // ---------------------------------------------------------------- P7 look-back #2: publish now, resolve in the next iteration
     const uint32_t n_txn_chunk = block_scan(
         n_mem, ms->warp_tot, [&](uint32_t i) { return (uint32_t)txn_cnt[i]; },
         [&](uint32_t i, uint32_t ex, uint32_t) { txn_loc[i] = (uint16_t)ex; });
     cta_publish2(P.state2, chunk, n_txn_chunk);
+    // Next ticket + prefetch of that chunk's text into the other buffer (free since the
+    // top-of-loop barrier).  Tickets must be taken in the order the chunks really start, or a
+    // chunk's predecessor could begin after the chunk itself and every look-back would wait for
+    // it: so as late as the prefetch latency allows, and after every wait of this iteration.
+    if (tid == 0) {
+      const uint32_t nxt = atomicAdd(&P.g->ticket, 1u);
+      ms->chunk_next = nxt;
+      if (TI_TEXT_BUFS == 2 && nxt < P.n_chunks) issue_bulk(nxt, buf ^ 1);
+      if (chunk == P.n_chunks - 1) {                   // last chunk: totals (transactions: finish_txn)
+        P.counters[kCntNInst + 0] = base_inst + n_inst; P.counters[kCntNInst + 1] = base_mem + n_mem;
+        P.counters[kCntNInst + 3] = base_tb + n_tb; P.counters[kCntNInst + 4] = base_warp + n_warp;
+        P.counters[kCntNInst + 7] = P.len;
+      }
+    }
 
     TI_STAMP(10);  // P7 scan + publish
     // ---------------------------------------------------------------- P6c parked headers and address rows out
@@ -459,10 +529,11 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         rp->mem_idx = (uint32_t)(row + P.off_mem);
       }
     }
-    __syncthreads();   // mem_idx of every record is final
+    __syncthreads();   // mem_idx of every record is final; chunk_next visible
 
     TI_STAMP(11);  // P6c
     // ---------------------------------------------------------------- P8 records out + counters
+    if (TI_TEXT_BUFS == 2 && ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, buf ^ 1);
     {
       const uint4 *src = reinterpret_cast<const uint4 *>(recs);
       uint4 *dst = reinterpret_cast<uint4 *>(P.inst + base_inst);
@@ -487,60 +558,20 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
 
     TI_STAMP(12);  // P8
-    // ---------------------------------------------------------------- P7' resolve look-back #2 + ordered copy-out
-    const uint64_t base_txn = cta_resolve2(P.state2, chunk, n_txn_chunk, ms->lb);
-    TI_STAMP(13);  // P7' resolve
-    if (TI_TEXT_BUFS == 2 && ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, buf ^ 1);   // visible after the barriers above
-    if (tid == 0) {
-      uint32_t ov = 0;
-      if (base_txn + n_txn_chunk > P.cap_txn) ov |= 4;
-      if (base_txn + n_txn_chunk > 0xfffffffeull) ov |= 32;
-      if (ov) atomicOr(&P.g->overflow, ov);
-      if (chunk == P.n_chunks - 1) {                   // last chunk: CSR sentinel + totals
-        if (base_mem + n_mem <= P.cap_mem) P.txn_off[base_mem + n_mem] = (uint32_t)(base_txn + n_txn_chunk + P.off_txn);
-        P.counters[kCntNInst + 0] = base_inst + n_inst; P.counters[kCntNInst + 1] = base_mem + n_mem;
-        P.counters[kCntNInst + 2] = base_txn + n_txn_chunk; P.counters[kCntNInst + 3] = base_tb + n_tb;
-        P.counters[kCntNInst + 4] = base_warp + n_warp; P.counters[kCntNInst + 7] = P.len;
-      }
+    // ---------------------------------------------------------------- P7' transactions out: now, or parked for the next iteration
+    // The staging area, txn_cnt / txn_slot / txn_loc stay untouched until the next chunk's P6a, so
+    // resolving look-back #2 can wait until then (half a chunk time of slack).  Not when staging
+    // overflowed: the recompute needs this chunk's records.
+    if (ms->stage_used > stage_cap) {
+      finish_txn(chunk, n_mem, n_txn_chunk, base_mem, true);
+    } else {
+      pend = true; pend_chunk = chunk; pend_n_mem = n_mem; pend_n_txn = n_txn_chunk; pend_base_mem = base_mem;
+      pend_stage_used = ms->stage_used;
     }
-    for (uint32_t mo = tid; mo < n_mem; mo += kThreads)
-      if (base_mem + mo < P.cap_mem) P.txn_off[base_mem + mo] = (uint32_t)(base_txn + txn_loc[mo] + P.off_txn);
-    // staged transactions -> HBM in file order: one thread moves one instruction's records
-    // (32 instructions per warp in flight; a warp per instruction left 3/4 of the lanes idle)
-    for (uint32_t mo = tid; mo < n_mem; mo += kThreads) {
-      const uint32_t n = txn_cnt[mo], slot = txn_slot[mo];
-      if (!n || slot == 0xFFFFu) continue;
-      const uint64_t at = base_txn + txn_loc[mo];
-      const uint4 *src = reinterpret_cast<const uint4 *>(stage + slot);
-      uint4 *dst = reinterpret_cast<uint4 *>(P.txn + at);
-      for (uint32_t k = 0; k < n; ++k)
-        if (at + k < P.cap_txn) { dst[2 * k] = src[2 * k]; dst[2 * k + 1] = src[2 * k + 1]; }
-    }
-    if (ms->stage_used > stage_cap) {                // warp-uniform: some instructions did not fit the staging area
-      for (uint32_t mo = wid; mo < n_mem; mo += kWarps) {
-        if (txn_slot[mo] != 0xFFFFu || !txn_cnt[mo]) continue;
-        // coalesce again from the row written in P6b / P6c
-        const uint64_t at = base_txn + txn_loc[mo];
-        const ti_inst_rec *rp = recs + mem_list[mo];
-        const uint64_t row = base_mem + mo;
-        const uint64_t addr = row < P.cap_mem ? __ldcg(P.rows + row * 32 + lane) : 0;
-        const unsigned ds = rp->data_size, pack_b = rp->pack_b, op = rp->op;
-        const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
-        const unsigned is_write = (op == OP_STORE || op == OP_TSTORE || (pack_b >> 4 & 3) == 2) ? 1u : 0u;
-        Txn t2[2];
-        unsigned pos[2] = {~0u, ~0u};
-        uint32_t fl = 0;
-        unsigned m;
-        if (pack_b >> 6 & 1) m = coalesce_atomic(P, rp->mask, addr, ds, seg, t2[0], pos[0], fl);
-        else m = coalesce_global(P, rp->mask, addr, ds, seg, t2, pos, wscratch);
-        const unsigned type = is_write ? 4u : 0u;
-        if (pos[0] < m && at + pos[0] < P.cap_txn) P.txn[at + pos[0]] = reduce_and_send(t2[0], seg, type, is_write);
-        if (pos[1] < m && at + pos[1] < P.cap_txn) P.txn[at + pos[1]] = reduce_and_send(t2[1], seg, type, is_write);
-      }
-    }
-    TI_STAMP(14);  // P7' copy-out
+    TI_STAMP(13);  // P7' (overflow only)
     if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }
   }
+  if (pend) finish_txn(pend_chunk, pend_n_mem, pend_n_txn, pend_base_mem, false);
   __syncthreads();
   flush_counters(cnt, P.counters);
 }

@@ -31,7 +31,7 @@ ms = k.decode_ms()
 tp.lib.ti_debug_phase_cycles(out)
 names = ["top/ticket/edges", "P0 wait text", "P1 line index", "P2 tokenize", "P3 mem ordinals", "P4 publish 1", "P5 structure",
          "P6a stride path", "P4' resolve 1", "P6b warp path", "P7 scan+publish 2", "P6c headers+rows out", "P8 records+counters",
-         "P7' resolve 2", "P7' copy-out"]
+         "P7' txns out (staging overflow)", "P7' txns out of previous chunk"]
 tot = sum(out[:15])
 print("decode %.3f ms; thread-0 cycles per phase (share of the CTA's time):" % ms)
 for n, v in zip(names, out):
