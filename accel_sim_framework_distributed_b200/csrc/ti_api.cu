@@ -725,7 +725,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
 // The only memory the decode needs beyond its inputs and outputs is the pair of
 // per-chunk look-back tables.  For this entry point they live in the file-scope device
 // array below instead of a cudaMalloc'ed buffer: (TI_NOALLOC_MAX_TEXT / chunk + 2)
-// entries of 32 + 8 bytes, about 0.65 MB, resident on every GPU that loads the library
+// entries of 32 + 8 bytes, about 0.9 MB, resident on every GPU that loads the library
 // for as long as the process lives.
 //
 // In host code the name `g_noalloc_scratch` is only a handle for the symbol, not an

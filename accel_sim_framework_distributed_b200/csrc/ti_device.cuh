@@ -42,19 +42,19 @@ namespace ti {
 
 // ------------------------------------------------------------------ tunables
 #ifndef TI_CHUNK
-#define TI_CHUNK 16384
+#define TI_CHUNK 12288
 #endif
 #ifndef TI_THREADS
-#define TI_THREADS 320
+#define TI_THREADS 256
 #endif
 #ifndef TI_TXN_STAGE
-#define TI_TXN_STAGE 768
+#define TI_TXN_STAGE 640
 #endif
 #ifndef TI_TEXT_BUFS
-#define TI_TEXT_BUFS 2     // 2 = prefetch the next chunk's text during P7/P8; 1 = load at the top of the chunk
+#define TI_TEXT_BUFS 1     // text buffers; the text is dead after P6b, so one buffer takes the prefetch of the next chunk too
 #endif
 #ifndef TI_MIN_BLOCKS
-#define TI_MIN_BLOCKS 2   // resident CTAs per SM the register allocation is bounded for
+#define TI_MIN_BLOCKS 3   // resident CTAs per SM the register allocation is bounded for
 #endif
 constexpr int kChunk = TI_CHUNK;        // bytes of text owned by one chunk
 constexpr int kThreads = TI_THREADS;    // threads per CTA

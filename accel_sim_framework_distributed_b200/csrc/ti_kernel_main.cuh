@@ -166,11 +166,10 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     if (chunk >= P.n_chunks) break;
     if (tid == 0) {
       ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
-      if (TI_TEXT_BUFS == 1 && iter) issue_bulk(chunk, 0);   // single buffer: it is free only now
     }
-    if (TI_TEXT_BUFS == 1 && iter) fill_edges(chunk, 0);
     __syncthreads();
     uint8_t *text = smem + oText + buf * kTextBytes;
+    const uint32_t *text32 = reinterpret_cast<const uint32_t *>(text);
     uint4 *text_v = reinterpret_cast<uint4 *>(text);
     const uint64_t cb = (uint64_t)chunk * kChunk;            // text offset of the chunk
     const uint32_t tbase = (uint32_t)(cb - 16);              // text offset = tbase + smem offset (mod 2^32)
@@ -313,40 +312,36 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
           [&](uint32_t i) { const unsigned c = text[sl_off[i]]; return (uint32_t)(c == 't' ? 1u : c == 'w' ? 0x10000u : 0u); },
           [&](uint32_t i, uint32_t ex, uint32_t) {
             const int o = sl_off[i];
-            int q = o;
             const unsigned c = text[o];
-            uint32_t fl = 0;
             // instruction lines before this one = its rank in the sorted inst_off list
             uint32_t lo = 0, hi = n_inst;
             while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (inst_off[mid] < o) lo = mid + 1; else hi = mid; }
             const uint64_t first_inst = inst0 + lo;
-            if (c == '#') {
-              if (match_lit(text, q, "#BEGIN_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 1], 1u);
-              else { q = o; if (match_lit(text, q, "#END_TB") && text[q] == '\n') atomicAdd(&cnt[kCntConst + 2], 1u); else fl = TI_EF_BAD_STRUCTURE; }
-            } else if (c == 't') {                        // trace_parser.cc:423-427
+            SlParsed sp = parse_struct_line(text, text32, o);
+            int32_t n = 0;
+            if (sp.type == SL_WARP) {                     // trace_parser.cc:428-437: the next non-blank line must be "insts = n"
+              int q = sp.q;
+              sp.ok = sp.ok && sp.v[0] >= 0;
+              while (text[q] == '\n' && q < 16 + kChunk + kSlack) ++q;
+              sp.ok = sp.ok && load8(text32, (unsigned)q) == kLitInsts0;
+              q += 8;
+              sp.ok = sp.ok && parse_i32(text, q, n) && text[q] == '\n' && n >= 0;
+            }
+            if (sp.type == SL_INSTS) sp.ok = sp.ok && sp.v[0] >= 0;
+            uint32_t fl = sp.ok ? 0u : (uint32_t)TI_EF_BAD_STRUCTURE;
+            if (sp.ok && sp.type != SL_TB && sp.type != SL_WARP)
+              atomicAdd(&cnt[kCntConst + (sp.type == SL_BEGIN ? 1 : sp.type == SL_END ? 2 : 4)], 1u);
+            if (c == 't') {                               // trace_parser.cc:423-427
               ti_tb_rec r;
-              if (match_lit(text, q, "thread block = ") && parse_i32(text, q, r.x) && text[q++] == ',' &&
-                  parse_i32(text, q, r.y) && text[q++] == ',' && parse_i32(text, q, r.z) && text[q] == '\n') {
-                r.text_off = cb - 16 + (uint64_t)o + P.off_text; r.line_len = (uint32_t)(q - o);
-                r.first_warp = (uint32_t)(warp0 + (ex >> 16)); r.first_inst = (uint32_t)first_inst;
-              } else { fl = TI_EF_BAD_STRUCTURE; r.text_off = cb - 16 + (uint64_t)o; r.x = r.y = r.z = 0; r.line_len = 0; r.first_warp = r.first_inst = 0; }
+              r.text_off = cb - 16 + (uint64_t)o + (sp.ok ? P.off_text : 0); r.line_len = sp.ok ? (uint32_t)(sp.q - o) : 0u;
+              r.x = sp.ok ? sp.v[0] : 0; r.y = sp.ok ? sp.v[1] : 0; r.z = sp.ok ? sp.v[2] : 0;
+              r.first_warp = sp.ok ? (uint32_t)(warp0 + (ex >> 16)) : 0u; r.first_inst = sp.ok ? (uint32_t)first_inst : 0u;
               if ((ex & 0xffff) < tb_room) tb_out[ex & 0xffff] = r;
-            } else if (c == 'w') {                        // trace_parser.cc:428-437
-              int32_t w = 0, n = 0;
-              bool ok = match_lit(text, q, "warp = ") && parse_i32(text, q, w) && text[q] == '\n' && w >= 0;
-              if (ok) {  // the next non-blank line must be "insts = n"
-                while (text[q] == '\n' && q < 16 + kChunk + kSlack) ++q;
-                ok = match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0;
-              }
-              if (!ok) { fl = TI_EF_BAD_STRUCTURE; w = n = 0; }
+            } else if (c == 'w') {
               ti_warp_rec r;  // written even when malformed so the table never holds uninitialised rows
-              r.warp_id = (uint32_t)w; r.n_insts = (uint32_t)n; r.first_inst = (uint32_t)first_inst; r.reserved = 0;
+              r.warp_id = sp.ok ? (uint32_t)sp.v[0] : 0u; r.n_insts = sp.ok ? (uint32_t)n : 0u; r.first_inst = (uint32_t)first_inst; r.reserved = 0;
               if ((ex >> 16) < warp_room) warp_out[ex >> 16] = r;
-            } else if (c == 'i') {
-              int32_t n = 0;
-              if (match_lit(text, q, "insts = ") && parse_i32(text, q, n) && text[q] == '\n' && n >= 0) atomicAdd(&cnt[kCntConst + 4], 1u);
-              else fl = TI_EF_BAD_STRUCTURE;
-            } else fl = TI_EF_BAD_STRUCTURE;
+            }
             if (line_end(nlmap32, (unsigned)o) - (unsigned)o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
             note_error(ms, fl, tbase + (uint32_t)o);
           });
@@ -387,6 +382,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       uint32_t slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
       if (slot + n_txn > stage_cap) slot = 0xFFFFu;
       txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
+      rp->mem_idx = mo;                                // chunk-relative until P8 adds the prefix
       if (n_txn && slot != 0xFFFFu) {
         const unsigned is_write = op == OP_STORE ? 1u : 0u;
         if (dense) dense_emit(d, ds, seg, is_write ? 4u : 0u, is_write, stage + slot);
@@ -456,7 +452,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       uint32_t slot = 0;
       if (lane == 0) {
         note_error(ms, fl, rp->opc_off);
-        rp->mem_idx = (uint32_t)(row + P.off_mem); rp->pack_c = (uint8_t)pack_c; rp->cycles = (uint8_t)cycles;
+        rp->mem_idx = mo; rp->pack_c = (uint8_t)pack_c; rp->cycles = (uint8_t)cycles;
         slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
         if (slot + n_txn > stage_cap) slot = 0xFFFFu;             // staging full: recomputed after look-back #2
         txn_cnt[mo] = (uint8_t)n_txn; txn_slot[mo] = (uint16_t)slot;
@@ -480,10 +476,15 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     // top-of-loop barrier).  Tickets must be taken in the order the chunks really start, or a
     // chunk's predecessor could begin after the chunk itself and every look-back would wait for
     // it: so as late as the prefetch latency allows, and after every wait of this iteration.
-    if (tid == 0) {
+    // The text is dead after P6b, so a single buffer can take the prefetch as well as a second one.
+    // A lane of the last warp (idle in P6c) waits for the atomic's round trip, not thread 0.
+    const unsigned nbuf = TI_TEXT_BUFS == 2 ? (buf ^ 1) : 0u;
+    if (tid == kThreads - 32) {
       const uint32_t nxt = atomicAdd(&P.g->ticket, 1u);
       ms->chunk_next = nxt;
-      if (TI_TEXT_BUFS == 2 && nxt < P.n_chunks) issue_bulk(nxt, buf ^ 1);
+      if (nxt < P.n_chunks) issue_bulk(nxt, nbuf);
+    }
+    if (tid == 0) {
       if (chunk == P.n_chunks - 1) {                   // last chunk: totals (transactions: finish_txn)
         P.counters[kCntNInst + 0] = base_inst + n_inst; P.counters[kCntNInst + 1] = base_mem + n_mem;
         P.counters[kCntNInst + 3] = base_tb + n_tb; P.counters[kCntNInst + 4] = base_warp + n_warp;
@@ -526,19 +527,20 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
 #pragma unroll 4
           for (unsigned l = 0; l < 32; l += 2) dst[l >> 1] = make_ulonglong2(stride_addr(d, l), stride_addr(d, l + 1));
         }
-        rp->mem_idx = (uint32_t)(row + P.off_mem);
       }
     }
-    __syncthreads();   // mem_idx of every record is final; chunk_next visible
 
     TI_STAMP(11);  // P6c
     // ---------------------------------------------------------------- P8 records out + counters
-    if (TI_TEXT_BUFS == 2 && ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, buf ^ 1);
     {
       const uint4 *src = reinterpret_cast<const uint4 *>(recs);
       uint4 *dst = reinterpret_cast<uint4 *>(P.inst + base_inst);
-      for (uint32_t k = tid; k < 2 * n_inst; k += kThreads)
-        if (base_inst + (k >> 1) < P.cap_inst) dst[k] = src[k];
+      const uint32_t mem0 = (uint32_t)(base_mem + P.off_mem);
+      for (uint32_t k = tid; k < 2 * n_inst; k += kThreads) {
+        uint4 v = src[k];
+        if (!(k & 1) && v.w != 0xFFFFFFFFu) v.w += mem0;   // mem_idx: chunk-relative ordinal -> file-global row
+        if (base_inst + (k >> 1) < P.cap_inst) dst[k] = v;
+      }
     }
     for (uint32_t io = tid; io < n_inst; io += kThreads) {
       const ti_inst_rec *rp = recs + io;
@@ -556,6 +558,9 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       atomicOr(&P.g->error_flags, ms->err);
       atomicMin(&P.g->first_error_off, ms->first_err);
     }
+
+    __syncthreads();   // chunk_next visible
+    if (ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, nbuf);
 
     TI_STAMP(12);  // P8
     // ---------------------------------------------------------------- P7' transactions out: now, or parked for the next iteration

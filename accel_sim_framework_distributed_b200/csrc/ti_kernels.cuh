@@ -349,6 +349,48 @@ TI_D bool parse_i32(const uint8_t *t, int &q, int32_t &v) {  // optional '-', <=
   return true;
 }
 
+// ---- structural lines ("#BEGIN_TB", "#END_TB", "thread block = x,y,z", "warp = w",
+// "insts = n"; trace_parser.cc:414-437): one convergent routine for all five shapes -- the
+// literal is compared as two 8-byte words under a length mask, then up to three
+// comma-separated integers follow -- so a warp holding a mix of them does not run one path
+// per shape.
+enum { SL_BEGIN = 0, SL_END = 1, SL_TB = 2, SL_WARP = 3, SL_INSTS = 4, SL_BAD = 5 };
+constexpr uint64_t lit_word(const char *s, int from, int len) {
+  uint64_t v = 0;
+  for (int i = 0; i < 8; ++i) if (from + i < len) v |= (uint64_t)(uint8_t)s[from + i] << (8 * i);
+  return v;
+}
+constexpr uint64_t kLitBegin0 = lit_word("#BEGIN_TB", 0, 9), kLitBegin1 = lit_word("#BEGIN_TB", 8, 9);
+constexpr uint64_t kLitEnd0 = lit_word("#END_TB", 0, 7);
+constexpr uint64_t kLitTb0 = lit_word("thread block = ", 0, 15), kLitTb1 = lit_word("thread block = ", 8, 15);
+constexpr uint64_t kLitWarp0 = lit_word("warp = ", 0, 7);
+constexpr uint64_t kLitInsts0 = lit_word("insts = ", 0, 8);
+struct SlParsed { unsigned type; int32_t v[3]; int q; bool ok; };
+
+TI_D SlParsed parse_struct_line(const uint8_t *text, const uint32_t *t32, int o) {
+  SlParsed r;
+  const unsigned c = text[o];
+  r.type = c == '#' ? (text[o + 1] == 'B' ? SL_BEGIN : SL_END) : c == 't' ? SL_TB : c == 'w' ? SL_WARP : c == 'i' ? SL_INSTS : SL_BAD;
+  const unsigned t = r.type;
+  const uint64_t l0 = t == SL_BEGIN ? kLitBegin0 : t == SL_END ? kLitEnd0 : t == SL_TB ? kLitTb0 : t == SL_WARP ? kLitWarp0 : kLitInsts0;
+  const uint64_t l1 = t == SL_BEGIN ? kLitBegin1 : t == SL_TB ? kLitTb1 : 0ull;
+  const unsigned len = t == SL_BEGIN ? 9u : t == SL_TB ? 15u : t == SL_INSTS ? 8u : 7u;
+  const unsigned nints = t == SL_TB ? 3u : (t == SL_WARP || t == SL_INSTS) ? 1u : 0u;
+  const uint64_t m0 = len >= 8 ? ~0ull : (1ull << (8 * len)) - 1, m1 = len > 8 ? (1ull << (8 * (len - 8))) - 1 : 0ull;
+  const uint64_t a0 = load8(t32, (unsigned)o), a1 = load8(t32, (unsigned)o + 8);
+  r.ok = t != SL_BAD && (((a0 ^ l0) & m0) | ((a1 ^ l1) & m1)) == 0;
+  r.q = o + (int)len;
+  r.v[0] = r.v[1] = r.v[2] = 0;
+#pragma unroll
+  for (unsigned k = 0; k < 3; ++k)
+    if (k < nints && r.ok) {
+      if (k) r.ok = text[r.q++] == ',';
+      r.ok = r.ok && parse_i32(text, r.q, r.v[k]);
+    }
+  r.ok = r.ok && text[r.q] == '\n';
+  return r;
+}
+
 }  // namespace ti
 
 #include "ti_kernel_main.cuh"
