@@ -192,3 +192,34 @@ int __syncthreads_and(int pred) {
   __syncthreads();
   return r;
 }
+
+// Named barriers: the first `n` arrivals at barrier `id` release each other.  The AND variant
+// is three rounds (vote, read, reset) like __syncthreads_and; the last thread to leave the
+// read round resets the accumulator.
+namespace emu {
+void named_bar_sync(unsigned id, unsigned n) {
+  if (id == 0) { __syncthreads(); return; }
+  Machine &m = M();
+  Cta &c = m.ctas[m.cur->cta];
+  const unsigned gen = c.nbar_gen[id];
+  if (++c.nbar_count[id] == n) {
+    c.nbar_count[id] = 0;
+    c.nbar_gen[id]++;
+    m.progress++;
+    return;
+  }
+  while (c.nbar_gen[id] == gen) yield_();
+}
+int named_bar_and(unsigned id, unsigned n, int pred) {
+  if (id == 0) return __syncthreads_and(pred);
+  Machine &m = M();
+  Cta &c = m.ctas[m.cur->cta];
+  if (!pred) c.nbar_and[id] = 0;
+  named_bar_sync(id, n);
+  const int r = c.nbar_and[id];
+  named_bar_sync(id, n);
+  c.nbar_and[id] = 1;       // every participant writes the same value; all have read
+  named_bar_sync(id, n);
+  return r;
+}
+}  // namespace emu

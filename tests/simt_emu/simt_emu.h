@@ -56,6 +56,9 @@ struct Cta {
   std::vector<Warp> warps;
   unsigned bar_count = 0, bar_gen = 0, live = 0;
   int and_acc = 1;
+  // named barriers (bar.sync id, n / bar.red.and id, n): id 1..15, n = participating threads
+  unsigned nbar_count[16] = {0}, nbar_gen[16] = {0};
+  int nbar_and[16] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};
 };
 
 struct Thread {
@@ -89,6 +92,10 @@ extern dim3 blockDim, gridDim;
 // ------------------------------------------------------------ synchronisation
 void __syncthreads();
 int __syncthreads_and(int pred);
+namespace emu {
+void named_bar_sync(unsigned id, unsigned n);
+int named_bar_and(unsigned id, unsigned n, int pred);
+}
 static inline void __syncwarp(unsigned mask = 0xffffffffu) { emu::collective(mask, emu::SYNCWARP, 0, 0); }
 static inline void __threadfence() {}
 static inline void __threadfence_block() {}
