@@ -1,0 +1,63 @@
+"""Multi-GPU host logic of the trace-ingest path: one process per GPU, no data-path collective.
+
+The reference has no distributed mode for this path (it is single-threaded C++,
+gpu-simulator/main.cc:60-190 walks the command list one kernel at a time).  The path
+shards at two levels:
+
+  level 1  kernel files of a kernelslist.g -> ranks   (kernels_for_rank)
+  level 2  byte ranges of one kernel file, cut at "\\n#BEGIN_TB" by ti_plan_shards
+           (shard_for_rank)
+
+Records, rows and transactions never cross ranks.  The only exchange is the integer
+AccelWattch counter block: summed as uint64 over all ranks (allreduce_counters), after
+which every rank derives bit-identical doubles with ti_counters_finalize.  torch.distributed
+is the plumbing: NCCL on GPUs (bench.py), gloo in the CPU tests.
+"""
+import numpy as np
+
+from . import records as R
+
+
+def kernels_for_rank(n_kernels, rank, world):
+    """Contiguous blocks of the command list's kernel launches, sizes differing by at most one
+    (contiguous rather than round-robin: a rank then owns one run of the list, and the k-th
+    thread block of the k-th kernel keeps its file order inside the rank)."""
+    if world <= 0 or not 0 <= rank < world:
+        raise ValueError("rank %r of world %r" % (rank, world))
+    base, extra = divmod(n_kernels, world)
+    lo = rank * base + min(rank, extra)
+    return list(range(lo, lo + base + (1 if rank < extra else 0)))
+
+
+def shard_for_rank(cuts, rank):
+    """(begin, end) byte range of `rank` from the world+1 cut points ti_plan_shards returned."""
+    if not 0 <= rank < len(cuts) - 1:
+        raise ValueError("rank %r with %d cut points" % (rank, len(cuts)))
+    return int(cuts[rank]), int(cuts[rank + 1])
+
+
+def allreduce_counters(counters, device=None, group=None):
+    """Sum one rank's ti_counters block (numpy record of dtype records.COUNTERS) over all
+    ranks; returns the summed record.  All fields are uint64 event counts, so the block is
+    reduced as one int64 vector (two's-complement addition is the same operation)."""
+    import torch
+    import torch.distributed as dist
+
+    block = np.zeros(1, dtype=R.COUNTERS)
+    block[0] = counters
+    vec = np.frombuffer(block.tobytes(), dtype=np.int64).copy()
+    t = torch.from_numpy(vec)
+    if device is not None:
+        t = t.to(device)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return np.frombuffer(t.cpu().numpy().tobytes(), dtype=R.COUNTERS)[0]
+
+
+def finalize(parser, counters):
+    """ti_counters_finalize through a trace_parser: integer block -> AccelWattch doubles."""
+    cnt = np.zeros(1, dtype=R.COUNTERS)
+    cnt[0] = counters
+    pw = np.zeros(1, dtype=R.POWER)
+    parser._ck(parser.lib.ti_counters_finalize(parser.ctx, cnt.ctypes.data, pw.ctypes.data))
+    return pw[0]

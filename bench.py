@@ -51,6 +51,16 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def traffic_bytes(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one ti_decode_kernel launch, from the committed
+    ncu --set full capture of this workload (never measured under the timed run); None if not captured."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(p):
+        return None
+    t = json.load(open(p)).get(workload)
+    return None if not t else int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons during the timed region."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
@@ -215,15 +225,13 @@ def bench_b200(args):
     # ---- NCCL all-reduce of the integer counter block (the path's only exchange), timed apart
     allreduce_ms = None
     if world > 1:
-        t = torch.from_numpy(np.frombuffer(cnt.tobytes(), dtype=np.int64).copy()).cuda()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        dist.all_reduce(t)  # warm-up
+        from accel_sim_framework_distributed_b200 import distributed as D
+        D.allreduce_counters(cnt, device="cuda")  # warm-up
         torch.cuda.synchronize()
-        t = torch.from_numpy(np.frombuffer(cnt.tobytes(), dtype=np.int64).copy()).cuda()
-        e0.record(); dist.all_reduce(t); e1.record()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); total_cnt = D.allreduce_counters(cnt, device="cuda"); e1.record()
         torch.cuda.synchronize()
         allreduce_ms = e0.elapsed_time(e1)
-        total_cnt = np.frombuffer(t.cpu().numpy().tobytes(), dtype=cnt.dtype)[0]
     else:
         total_cnt = cnt
 
@@ -270,7 +278,7 @@ def bench_b200(args):
                        "sharding": "one kernel file per GPU, no data-path collective; counters all-reduced (NCCL) after the timed region"},
             "warp_insts_per_s": all_inst * args.steps / (total_ms * 1e-3),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "frac_of_nominal_8TBs": achieved / 8000.0, "traffic": None, "peak_source": peak_src,
+                         "frac_of_nominal_8TBs": achieved / 8000.0, "traffic": traffic_bytes(args.workload), "traffic_unit": "dram bytes per launch (ncu, profiles/ncu_traffic.json)", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": b_alg, "kernel": "ti_decode_kernel", "launch_ms": per_launch_ms},
             "e2e": {"value": all_bytes / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": len(body), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": e2e_s * 1e3, "warp_insts_per_s": all_inst / e2e_s},
