@@ -116,6 +116,15 @@ def test_full_size_properties(cuda_parser):
     inst1, txn1 = d.inst.copy(), d.txn.copy()
     d2 = k.run()
     assert np.array_equal(inst1, d2.inst) and np.array_equal(txn1, d2.txn)
+    # the pipelined host-to-host entry point returns the same bytes as the one-piece path
+    rows1, off1, tb1, warp1 = d2.rows.copy(), d2.txn_off.copy(), d2.tb.copy(), d2.warp.copy()
+    cnt1 = np.array(d2.counters, dtype=T.COUNTERS)
+    d3 = k.run_streamed(32 << 20)
+    assert np.array_equal(inst1, d3.inst) and np.array_equal(txn1, d3.txn) and np.array_equal(rows1, d3.rows)
+    assert np.array_equal(off1, d3.txn_off) and np.array_equal(tb1, d3.tb) and np.array_equal(warp1, d3.warp)
+    for f in T.COUNTERS.names:
+        if f not in ("reserved", "text_bytes"):
+            assert np.array_equal(cnt1[f], d3.counters[f]), f
     cuda_parser.kernel_finalizer(k)
 
 
