@@ -72,6 +72,11 @@ class NoAllocIO(C.Structure):
 TI_NOALLOC_MAX_TEXT = 256 << 20
 
 
+class RegroupStats(C.Structure):
+    _fields_ = [("n_lines", C.c_uint64), ("n_keys", C.c_uint64), ("out_bytes", C.c_uint64), ("n_tb_written", C.c_uint32),
+                ("n_tb_empty", C.c_uint32), ("n_warp_empty", C.c_uint32), ("device_ms", C.c_float)]
+
+
 class Command(C.Structure):
     _fields_ = [("kind", C.c_int32), ("line_off", C.c_uint32), ("line_len", C.c_uint32)]
 
@@ -83,6 +88,7 @@ SYMBOLS = [
     "ti_kernel_close", "ti_kernel_upload", "ti_kernel_decode", "ti_kernel_sync", "ti_kernel_fetch",
     "ti_kernel_dev_view", "ti_kernel_counters", "ti_counters_add", "ti_counters_finalize", "ti_kernel_timing",
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
+    "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist",
 ]
 
 
@@ -127,6 +133,9 @@ def load_library(path=None):
         "ti_parse_memcpy": (C.c_int, [V, S, P(U64), P(U64)]),
         "ti_decode_noalloc": (C.c_int, [V, P(NoAllocIO), V]),
         "ti_kernel_decode_streamed": (C.c_int, [V, S, P(View)]),
+        "ti_regroup_device": (C.c_int, [V, V, S, V, S, P(S), P(RegroupStats)]),
+        "ti_regroup_buffer": (C.c_int, [V, V, S, P(V), P(S), P(RegroupStats)]),
+        "ti_regroup_commandlist": (C.c_int, [C.c_char_p, S, C.c_char_p, S, P(S)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -145,5 +154,5 @@ def np_view(ptr, dtype, n, shape=None):
     return a.reshape(shape) if shape else a
 
 
-__all__ = ["load_library", "NoAllocIO", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "DevView", "Command", "TraceIngestError", "np_view",
+__all__ = ["load_library", "NoAllocIO", "RegroupStats", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "DevView", "Command", "TraceIngestError", "np_view",
            "SYMBOLS", "EF", "R"]

@@ -234,6 +234,30 @@ class trace_parser:  # noqa: N801 -- the reference's class name (trace_parser.h:
     def kernel_finalizer(self, kernel):
         kernel.close()
 
+    # post-traces-processing.cpp:85-194 (writer side)
+    def regroup(self, trace):
+        """kernel-N.trace image (bytes / numpy uint8) -> (kernel-N.traceg image as bytes, RegroupStats)."""
+        buf = np.frombuffer(trace, dtype=np.uint8) if not isinstance(trace, np.ndarray) else np.ascontiguousarray(trace, dtype=np.uint8)
+        out, n, st = C.c_void_p(), C.c_size_t(), _ffi.RegroupStats()
+        self._ck(self.lib.ti_regroup_buffer(self.ctx, buf.ctypes.data if len(buf) else None, len(buf), C.byref(out), C.byref(n), C.byref(st)))
+        return C.string_at(out.value, n.value), st
+
+    def regroup_device(self, dev_ptr, nbytes, out_ptr=None, cap=0):
+        """Device-resident variant: returns (out_len, RegroupStats); the text goes to out_ptr when given."""
+        n, st = C.c_size_t(), _ffi.RegroupStats()
+        self._ck(self.lib.ti_regroup_device(self.ctx, C.c_void_p(dev_ptr), nbytes, C.c_void_p(out_ptr) if out_ptr else None, cap, C.byref(n), C.byref(st)))
+        return n.value, st
+
+    # post-traces-processing.cpp:44-83
+    def regroup_commandlist(self, text):
+        n = C.c_size_t()
+        st = self.lib.ti_regroup_commandlist(text, len(text), None, 0, C.byref(n))
+        if st not in (0, 6):
+            self._ck(st)
+        out = C.create_string_buffer(max(1, n.value))
+        self._ck(self.lib.ti_regroup_commandlist(text, len(text), out, n.value, C.byref(n)))
+        return out.raw[:n.value]
+
     def plan_shards(self, body, n):
         body = np.ascontiguousarray(body, dtype=np.uint8)
         cuts = (C.c_size_t * (n + 1))()

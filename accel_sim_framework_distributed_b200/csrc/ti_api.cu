@@ -77,8 +77,12 @@ int arch_column(unsigned v) {  // trace_driven.cc:100-118
 
 }  // namespace
 
+struct ti_regroup_state;
+static void regroup_state_free(ti_regroup_state *s);
+
 struct ti_ctx {
   ti_config cfg;
+  ti_regroup_state *rg = nullptr;   // workspace of ti_regroup_* (allocated on first use)
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   ti::IsaSlot *d_isa[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -178,6 +182,7 @@ ti_status ti_ctx_create(const ti_config *cfg, ti_ctx **out) {
 
 void ti_ctx_destroy(ti_ctx *c) {
   if (!c) return;
+  regroup_state_free(c->rg);
   for (auto &p : c->d_isa) if (p) cudaFree(p);
   if (c->d_spop) cudaFree(c->d_spop);
   if (c->ev0) cudaEventDestroy(c->ev0);
@@ -825,6 +830,8 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
   }
   return TI_OK;
 }
+
+#include "ti_regroup_api.inc"
 
 #if defined(TI_PHASE_TIMING) && !defined(TI_EMU)
 // tuning builds only: read and reset the per-phase cycle sums

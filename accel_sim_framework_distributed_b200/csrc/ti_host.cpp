@@ -6,6 +6,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
 
 #include "../../include/traceingest.h"
@@ -230,5 +231,30 @@ ti_status ti_counters_finalize_cfg(const ti_config *cfg, const ti_counters *c, t
   o->n_tex_insn = (double)(c->space_lanes[9][0] + c->space_lanes[9][1]);
   o->n_load_insn = (double)(c->space_lanes[11][0] + c->space_lanes[2][0]);
   o->n_store_insn = (double)(c->space_lanes[11][1] + c->space_lanes[2][1]);
+  return TI_OK;
+}
+
+// post-traces-processing.cpp:44-83: kernelslist -> kernelslist.g
+extern "C" ti_status ti_regroup_commandlist(const char *text, size_t len, char *out, size_t cap, size_t *out_len) {
+  if ((!text && len) || !out_len) return TI_ERR_INVALID_ARG;
+  size_t need = 0, p = 0;
+  auto put = [&](const char *s, size_t n) { if (out && need + n <= cap) memcpy(out + need, s, n); need += n; };
+  // while (!eof) getline: every '\n'-terminated piece plus the (possibly empty) rest
+  while (p <= len) {
+    const char *nl = p < len ? (const char *)memchr(text + p, '\n', len - p) : nullptr;
+    const size_t e = nl ? (size_t)(nl - text) : len;
+    const size_t n = e - p;
+    if (n) {
+      const char *l = text + p;
+      if (n >= 6 && !memcmp(l, "Memcpy", 6)) { put(l, n); put("\n", 1); }
+      else if (n >= 6 && !memcmp(l, "kernel", 6)) { put(l, n); put("g\n", 2); }
+      else if (n >= 4 && !memcmp(l, "nccl", 4)) { put(l, n); put("\n", 1); }
+      else { ti::set_error("Undefined command: %.*s", (int)std::min<size_t>(n, 200), l); *out_len = need; return TI_ERR_PARSE; }
+    }
+    if (!nl) break;
+    p = e + 1;
+  }
+  *out_len = need;
+  if (need > cap || (!out && need)) { ti::set_error("kernelslist.g needs %zu bytes", need); return TI_ERR_CAPACITY; }
   return TI_OK;
 }

@@ -49,5 +49,21 @@ def main():
         print(name, len(img), r.stdout.strip())
 
 
+def regroup_fixtures():
+    """Raw kernel-N.trace inputs + what the REFERENCE's post-traces-processing.cpp (oracle/_ref/ptp_ref)
+    writes for them: the pin of ti_regroup_* and of rawtrace.ptp_port."""
+    import tempfile
+    import rawtrace
+    import test_regroup
+    for name in ("soup", "grid_y", "empty_blocks", "blank_lines_inside", "no_trailing_newline", "header_only", "one_line"):
+        raw = test_regroup.CASES[name]
+        with tempfile.TemporaryDirectory() as tmp:
+            g, _, out = rawtrace.ptp_reference(raw, tmp)
+        open(os.path.join(HERE, "regroup_%s.trace" % name), "wb").write(raw)
+        open(os.path.join(HERE, "regroup_%s.traceg" % name), "wb").write(g)
+        print("regroup_" + name, len(raw), len(g), out.count("Warning"), "warnings")
+
+
 if __name__ == "__main__":
+    regroup_fixtures()
     main()

@@ -20,12 +20,13 @@ class GenParams(C.Structure):
         ("seed", C.c_uint64), ("profile", C.c_uint32), ("grid", C.c_uint32 * 3), ("block", C.c_uint32 * 3),
         ("insts_per_warp", C.c_uint32), ("binary_version", C.c_uint32), ("kernel_id", C.c_uint32),
         ("trace_version", C.c_uint32), ("n_threads", C.c_uint32), ("variant", C.c_uint32),
-        ("shmem_base", C.c_uint64), ("local_base", C.c_uint64),
+        ("shmem_base", C.c_uint64), ("local_base", C.c_uint64), ("raw", C.c_uint32), ("pad_", C.c_uint32),
     ]
 
 
 def _gen_lib():
-    if not os.path.exists(GEN):
+    src = os.path.join(ROOT, "tools", "tigen.cc")
+    if not os.path.exists(GEN) or (os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(GEN)):
         subprocess.run(["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-o", GEN,
                         os.path.join(ROOT, "tools", "tigen.cc"), "-lpthread"], check=True)
     lib = C.CDLL(GEN)
@@ -35,7 +36,7 @@ def _gen_lib():
 
 
 def generate_bytes(profile, seed, n_tb, insts_per_warp, binary_version=70, block_threads=256, trace_version=3,
-                   variant=0, kernel_id=1, grid=None, block=None, size_hint=None,
+                   variant=0, kernel_id=1, grid=None, block=None, size_hint=None, raw=0,
                    shmem_base=0x00007f8c00000000, local_base=0x00007f8c10000000):
     """Returns the whole .traceg image as a numpy uint8 array."""
     lib = _gen_lib()
@@ -47,6 +48,7 @@ def generate_bytes(profile, seed, n_tb, insts_per_warp, binary_version=70, block
         p.grid[i], p.block[i] = g[i], b[i]
     p.binary_version, p.kernel_id, p.trace_version, p.variant = binary_version, kernel_id, trace_version, variant
     p.shmem_base, p.local_base = shmem_base, local_base
+    p.raw = raw
     cap = size_hint or 0
     buf = np.empty(max(cap, 1), dtype=np.uint8)
     n = lib.tigen_generate(C.byref(p), buf.ctypes.data if cap else None, cap)

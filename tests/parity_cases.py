@@ -32,7 +32,7 @@ def check_against_dump(d, o, offsets, skip_counters=("reserved", "n_begin_tb", "
 
 
 def golden_names():
-    return sorted(os.path.basename(p)[:-7] for p in glob.glob(os.path.join(GOLDEN, "*.traceg")))
+    return sorted(os.path.basename(p)[:-7] for p in glob.glob(os.path.join(GOLDEN, "*.traceg")) if os.path.exists(p[:-7] + ".tidump"))
 
 
 def run_golden(tp, name):

@@ -37,6 +37,9 @@ typedef struct tigen_params {
   uint32_t n_threads;      // generator threads (0 = hardware concurrency)
   uint32_t variant;        // profile-specific (profile 1: 0 layerforward, 1 adjust_weights)
   uint64_t shmem_base, local_base;
+  uint32_t raw;            // 1: the tracer's raw kernel-N.trace layout (every line prefixed "tbx tby tbz warp", the warps of a
+                           //    thread block interleaved, no block structure) -- the input of post-traces-processing
+  uint32_t pad_;
 } tigen_params;
 size_t tigen_generate(const tigen_params *p, char *buf, size_t cap);
 }
@@ -137,7 +140,7 @@ struct Ctx {
 };
 
 void line_prefix(Out &o, const Ctx &c, uint32_t bx, uint32_t by, uint32_t bz, uint32_t w, uint32_t pc, uint32_t mask) {
-  if (c.p->trace_version < 3) o.put("%u %u %u %u ", bx, by, bz, w);
+  if (c.p->trace_version < 3 || c.p->raw) o.put("%u %u %u %u ", bx, by, bz, w);
   o.put("%04x %08x ", pc, mask);
 }
 
@@ -461,6 +464,9 @@ extern "C" size_t tigen_generate(const tigen_params *pp, char *buf, size_t cap) 
     for (uint64_t tb = lo; tb < hi; ++tb) {
       uint32_t bx = (uint32_t)(tb % p.grid[0]), by = (uint32_t)(tb / p.grid[0] % p.grid[1]),
                bz = (uint32_t)(tb / ((uint64_t)p.grid[0] * p.grid[1]));
+      Out tmp;
+      Out &dst = o;
+      Out &o = p.raw ? tmp : dst;
       o.put("\n#BEGIN_TB\n\nthread block = %u,%u,%u\n", bx, by, bz);
       switch (p.profile) {
         case 1: gen_tb_backprop(o, c, (uint32_t)tb, bx, by, bz); break;
@@ -471,6 +477,24 @@ extern "C" size_t tigen_generate(const tigen_params *pp, char *buf, size_t cap) 
         default: gen_tb_stream(o, c, (uint32_t)tb, bx, by, bz); break;
       }
       o.put("\n#END_TB\n");
+      if (p.raw) {  // keep only the instruction lines, round-robin over the warps (instruction k of every warp, then k+1 ...)
+        std::vector<std::vector<std::pair<size_t, size_t>>> per_warp;
+        const std::string &t = tmp.s;
+        for (size_t a = 0; a < t.size();) {
+          size_t e = t.find('\n', a);
+          if (e == std::string::npos) e = t.size();
+          if (e > a) {
+            if (!t.compare(a, 7, "warp = ")) per_warp.emplace_back();
+            else if (t[a] >= '0' && t[a] <= '9' && !per_warp.empty()) per_warp.back().emplace_back(a, e - a);
+          }
+          a = e + 1;
+        }
+        size_t most = 0;
+        for (auto &w : per_warp) most = std::max(most, w.size());
+        for (size_t k = 0; k < most; ++k)
+          for (auto &w : per_warp)
+            if (k < w.size()) { dst.s.append(t, w[k].first, w[k].second); dst.s.push_back('\n'); }
+      }
     }
   };
   std::vector<std::thread> th;
@@ -479,13 +503,13 @@ extern "C" size_t tigen_generate(const tigen_params *pp, char *buf, size_t cap) 
   for (auto &t : th) t.join();
   Out hdr;
   gen_header(hdr, p);
-  size_t total = hdr.s.size() + 1;  // trailing blank line, as post-traces-processing leaves one
+  size_t total = hdr.s.size() + (p.raw ? 0 : 1);  // trailing blank line, as post-traces-processing leaves one
   for (auto &o : parts) total += o.s.size();
   if (total > cap || !buf) return total;
   size_t off = 0;
   memcpy(buf + off, hdr.s.data(), hdr.s.size()); off += hdr.s.size();
   for (auto &o : parts) { memcpy(buf + off, o.s.data(), o.s.size()); off += o.s.size(); }
-  buf[off++] = '\n';
+  if (!p.raw) buf[off++] = '\n';
   return off;
 }
 
