@@ -1,15 +1,18 @@
-// The fused trace-ingest kernel (see ti_device.cuh for the data layout and the plan).
+// The fused trace-ingest kernel (see ti_device.cuh for the data layout, DESIGN.md 3 for the plan).
 //
 // Per chunk, one CTA runs these phases entirely out of shared memory:
-//   P0 stage-in   16 B vector loads of [chunk-16, chunk+CHUNK+slack) -> smem
-//   P1 line index newline bitmap (SIMD byte compare) -> line-start lists, by class
-//   P2 tokenize   thread-per-line decode of instruction lines -> 32 B records (smem)
-//   P3 compact    ordinal of every memory instruction (ballot scans)
-//   P4 look-back  chained scan #1 -> global offsets for inst / mem / tb / warp
-//   P5 structure  "thread block" / "warp"+"insts" / "#BEGIN_TB" / "#END_TB" lines
-//   P6 memory     warp-per-instruction: addresses -> 256 B row, coalescer -> smem
-//   P7 look-back  chained scan #2 over transaction counts, ordered copy-out
-//   P8 stage-out  records smem -> HBM with 16 B coalesced stores, counters
+//   P0  stage-in    TMA bulk copy of [chunk-16, chunk+CHUNK+slack) -> smem, prefetched one chunk ahead
+//   P1  line index  newline + delimiter bitmaps (SWAR) -> line-start lists, by class
+//   P2  tokenize    thread-per-line decode of instruction lines -> 32 B records (smem)
+//   P3  compact     ordinal of every memory instruction, base+stride / other lists
+//   P4  publish #1  (n_inst, n_mem, n_tb, n_warp) of the chunk for the chained scan
+//   P5  structure   "thread block" / "warp"+"insts" / "#BEGIN_TB" / "#END_TB" lines, parked chunk-relative
+//   P7' previous    look-back #2 of the PREVIOUS chunk resolves, its transactions leave in file order
+//   P6a stride      thread-per-instruction closed-form coalescing of base+stride lines -> smem
+//   P4' resolve #1  decoupled look-back -> global offsets for inst / mem / tb / warp
+//   P6b memory      warp-per-instruction: list / delta addresses -> 256 B row, coalescer -> smem
+//   P7  publish #2  scan of transaction counts, publish; next ticket + prefetch
+//   P6c / P8        parked headers, base+stride rows, records smem -> HBM; counters
 #ifndef TI_KERNELS_CUH
 #define TI_KERNELS_CUH
 
@@ -108,9 +111,6 @@ TI_D void mbar_wait(uint64_t *b, unsigned parity) {
 TI_D void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 #endif
 
-TI_D uint32_t ld_flag(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
-TI_D uint32_t ld_vol(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
-TI_D uint64_t ld_vol(const uint64_t *p) { return *reinterpret_cast<const volatile uint64_t *>(p); }
 
 TI_D uint64_t warp_sum_u64(uint64_t v) {
 #pragma unroll
@@ -126,64 +126,7 @@ TI_D uint64_t warp_sum_u64(uint64_t v) {
 TI_D unsigned long long ld_vol64(const unsigned long long *p) { return *reinterpret_cast<const volatile unsigned long long *>(p); }
 TI_D void st_vol64(unsigned long long *p, unsigned long long v) { *reinterpret_cast<volatile unsigned long long *>(p) = v; }
 
-TI_D void lookback1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64_t (&excl)[4]) {
-  const unsigned lane = lane_id();
-  if (lane == 0)
-    st_vol64(&st[c].agg, kValid | (unsigned long long)agg[3] << 42 | (unsigned long long)agg[2] << 28 |
-                             (unsigned long long)agg[1] << 14 | agg[0]);
-  excl[0] = excl[1] = excl[2] = excl[3] = 0;
-  for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= 32) {
-    const int64_t j = idx - lane;
-    unsigned long long A = kValid, I0 = kValid, I1 = kValid;  // chunks before the first: inclusive prefix 0
-    for (;;) {
-      if (j >= 0) { I0 = ld_vol64(&st[j].inc0); I1 = ld_vol64(&st[j].inc1); A = ld_vol64(&st[j].agg); }
-      const bool ready = ((I0 & I1) | A) >> 63;
-      if (__all_sync(kFull, ready)) break;
-      __nanosleep(64);
-    }
-    const bool hasinc = (I0 & I1) >> 63;
-    const uint32_t have = __ballot_sync(kFull, hasinc);
-    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
-    const bool useagg = lane < L;                      // A is valid for these lanes
-    excl[0] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A & 0x3fff) : 0u);
-    excl[1] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 14 & 0x3fff) : 0u);
-    excl[2] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 28 & 0x3fff) : 0u);
-    excl[3] += __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 42 & 0x3fff) : 0u);
-    if (L < 32) {
-      const unsigned long long i0 = __shfl_sync(kFull, I0, L), i1 = __shfl_sync(kFull, I1, L);
-      excl[0] += i0 & 0x7fffffffull; excl[1] += i0 >> 31 & 0x7fffffffull;
-      excl[2] += i1 & 0x7fffffffull; excl[3] += i1 >> 31 & 0x7fffffffull;
-      break;
-    }
-  }
-  if (lane == 0) {
-    st_vol64(&st[c].inc0, kValid | (excl[1] + agg[1]) << 31 | (excl[0] + agg[0]));
-    st_vol64(&st[c].inc1, kValid | (excl[3] + agg[3]) << 31 | (excl[2] + agg[2]));
-  }
-}
-
-TI_D uint64_t lookback2(State2 *st, uint32_t c, uint32_t agg) {
-  const unsigned lane = lane_id();
-  if (lane == 0 && c) st_vol64(&st[c].w, kAggValid | agg);
-  uint64_t excl = 0;
-  for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= 32) {
-    const int64_t j = idx - lane;
-    unsigned long long W = kValid;
-    for (;;) {
-      if (j >= 0) W = ld_vol64(&st[j].w);
-      if (__all_sync(kFull, (W >> 62) != 0)) break;
-      __nanosleep(64);
-    }
-    const uint32_t have = __ballot_sync(kFull, (W >> 63) != 0);
-    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
-    excl += __reduce_add_sync(kFull, lane < L ? (uint32_t)(W & 0xffffffffull) : 0u);
-    if (L < 32) { excl += __shfl_sync(kFull, W, L) & 0x3fffffffffffffffull; break; }
-  }
-  if (lane == 0) st_vol64(&st[c].w, kValid | (excl + agg));
-  return excl;
-}
-
-// ---- CTA-wide variants: thread t inspects chunk c-1-t, so one round covers kThreads
+// ---- CTA-wide look-back: thread t inspects chunk c-1-t, so one round covers kThreads
 // predecessors.  The persistent CTAs run phase-locked (equal work per chunk), so a chunk's
 // predecessors publish their aggregates at about the same moment as the chunk itself and
 // their inclusive prefixes only after their own look-back: the nearest inclusive prefix is
@@ -333,10 +276,6 @@ TI_D unsigned line_end(const uint32_t *nlmap32, unsigned o) {
   return (w << 5) + __ffs(bits) - 1;
 }
 
-TI_D bool match_lit(const uint8_t *t, int &q, const char *s) {
-  for (; *s; ++s, ++q) if (t[q] != (uint8_t)*s) return false;
-  return true;
-}
 TI_D bool parse_i32(const uint8_t *t, int &q, int32_t &v) {  // optional '-', <= 10 digits, fits int32
   const bool neg = t[q] == '-';
   if (neg) ++q;
