@@ -88,7 +88,7 @@ SYMBOLS = [
     "ti_kernel_close", "ti_kernel_upload", "ti_kernel_decode", "ti_kernel_sync", "ti_kernel_fetch",
     "ti_kernel_dev_view", "ti_kernel_counters", "ti_counters_add", "ti_counters_finalize", "ti_kernel_timing",
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
-    "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist",
+    "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets",
 ]
 
 
@@ -136,6 +136,7 @@ def load_library(path=None):
         "ti_regroup_device": (C.c_int, [V, V, S, V, S, P(S), P(RegroupStats)]),
         "ti_regroup_buffer": (C.c_int, [V, V, S, P(V), P(S), P(RegroupStats)]),
         "ti_regroup_commandlist": (C.c_int, [C.c_char_p, S, C.c_char_p, S, P(S)]),
+        "ti_regroup_buckets": (C.c_int, [V, P(V), P(V), P(U64), P(C.c_uint32)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -194,3 +194,44 @@ def test_gpu_regroup_large_properties(cuda_parser):
         with tempfile.TemporaryDirectory() as tmp:
             want, _, _ = rawtrace.ptp_reference(raw.tobytes(), tmp)
         assert got == want
+
+
+# ------------------------------------------------------------------ the drop-in command-line tool
+def _tool_matches_reference(lib_path, tmp):
+    """shim/post_traces_processing_b200.cc against the reference binary: same files, same stdout."""
+    import shutil
+    import subprocess
+    libdir, libname = os.path.split(lib_path)
+    tool = os.path.join(tmp, "ptp_b200")
+    subprocess.run(["g++", "-std=c++17", "-O2", "-w", "-I" + os.path.join(harness.ROOT, "include"), "-o", tool,
+                    os.path.join(harness.ROOT, "shim", "post_traces_processing_b200.cc"),
+                    "-L" + libdir, "-l:" + libname, "-Wl,-rpath," + libdir], check=True)
+    klist = "MemcpyHtoD,0x00007f2a00000000,65536\nncclCommInitAll\nkernel-1.trace\n\nkernel-2.trace\nkernel-9.trace\nncclCommDestroy\nfrobnicate\nkernel-3.trace\n"
+    outs = []
+    for who, exe in (("ref", rawtrace.PTP_REF), ("b200", tool)):
+        d = os.path.join(tmp, who, "traces")
+        os.makedirs(d)
+        open(os.path.join(d, "kernel-1.trace"), "wb").write(CASES["empty_blocks"])       # warnings for blocks and warps
+        open(os.path.join(d, "kernel-2.trace"), "wb").write(CASES["grid_y"])
+        open(os.path.join(d, "kernel-3.trace"), "wb").write(CASES["soup"])              # after the unknown command: never reached
+        open(os.path.join(d, "kernelslist"), "w").write(klist)                           # kernel-9.trace does not exist
+        r = subprocess.run([exe, "traces/kernelslist"], cwd=os.path.join(tmp, who), capture_output=True)
+        assert r.returncode == 0, (who, r.stderr[-400:])
+        files = {f: open(os.path.join(d, f), "rb").read() for f in sorted(os.listdir(d))}
+        outs.append((r.stdout, files))
+    assert outs[0][0] == outs[1][0]                       # stdout: "Processing file", warnings, "Undefined command"
+    assert b"Warning: Thread block" in outs[0][0] and b"Warning: Warp" in outs[0][0] and b"Undefined command" in outs[0][0]
+    assert sorted(outs[0][1]) == sorted(outs[1][1]) and "kernel-1.traceg" in outs[0][1] and "kernel-3.traceg" not in outs[0][1]
+    for f in outs[0][1]:
+        assert outs[0][1][f] == outs[1][1][f], f
+
+
+@pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref/ptp_ref not built (needs /root/reference)")
+def test_tool_matches_reference_emulated(tmp_path):
+    _tool_matches_reference(harness.emu_library(), str(tmp_path))
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref/ptp_ref not built (needs /root/reference)")
+def test_tool_matches_reference_cuda(tmp_path):
+    _tool_matches_reference(harness.CUDA_LIB, str(tmp_path))
