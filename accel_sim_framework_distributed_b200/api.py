@@ -132,6 +132,20 @@ class KernelTrace:
         self._next_tb = 0
         return d
 
+    def coalesce_local(self, local_map, issues):
+        """issues: numpy array of dtype records.LOCAL_ISSUE (inst, sid, tid0).  Returns (txn, txn_off)."""
+        issues = np.ascontiguousarray(issues, dtype=R.LOCAL_ISSUE)
+        n = len(issues)
+        off = np.zeros(n + 1, dtype=np.uint32)
+        n_txn = C.c_size_t()
+        lib = self._p.lib
+        st = lib.ti_kernel_coalesce_local(self._h, C.byref(local_map), issues.ctypes.data, n, None, 0, off.ctypes.data, C.byref(n_txn))
+        if st not in (0, 6):
+            self._p._ck(st)
+        txn = np.zeros(max(1, n_txn.value), dtype=R.TXN)
+        self._p._ck(lib.ti_kernel_coalesce_local(self._h, C.byref(local_map), issues.ctypes.data, n, txn.ctypes.data, len(txn), off.ctypes.data, C.byref(n_txn)))
+        return txn[:n_txn.value], off
+
     def close(self):
         if self._h:
             self._p.lib.ti_kernel_close(self._h)

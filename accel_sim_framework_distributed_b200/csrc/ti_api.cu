@@ -832,6 +832,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
 }
 
 #include "ti_regroup_api.inc"
+#include "ti_local_api.inc"
 
 #if defined(TI_PHASE_TIMING) && !defined(TI_EMU)
 // tuning builds only: read and reset the per-phase cycle sums

@@ -75,3 +75,6 @@ def qv100_config(**over):
     for k, v in over.items():
         c[k] = v
     return c
+
+# ti_local_issue
+LOCAL_ISSUE = np.dtype([("inst", "<u4"), ("sid", "<u4"), ("tid0", "<u4")])

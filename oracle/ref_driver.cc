@@ -90,16 +90,64 @@ static ti_config load_cfg(const char *path) {
   return cfg;
 }
 
+// shader_core_ctx::translate_local_memaddr (shader.cc:1714-1783) restated: shader.cc cannot be
+// linked here (it is the whole timing model).  `m_sid`, the two kernel_* members and m_config are
+// parameters; an assert of the original makes the function return ~0u.
+struct local_map_t { unsigned num_shader, n_thread_per_shader, local_mem_map, padded_threads_per_cta, max_cta_per_shader; };
+static unsigned translate_local_memaddr_restated(const local_map_t &m, unsigned m_sid, address_type localaddr, unsigned tid,
+                                                 unsigned datasize, new_addr_type *translated_addrs) {
+  address_type thread_base = 0;
+  unsigned max_concurrent_threads = 0;
+  if (m.local_mem_map) {
+    thread_base = 4 * (m.padded_threads_per_cta * (m_sid + m.num_shader * (tid / m.padded_threads_per_cta)) + tid % m.padded_threads_per_cta);
+    max_concurrent_threads = m.padded_threads_per_cta * m.max_cta_per_shader * m.num_shader;
+  } else {
+    thread_base = 4 * (m.n_thread_per_shader * m_sid + tid);
+    max_concurrent_threads = m.num_shader * m.n_thread_per_shader;
+  }
+  if (!(thread_base < 4 * max_concurrent_threads)) return ~0u;
+  unsigned num_accesses = 0;
+  if (datasize >= 4) {
+    if (datasize % 4 != 0) return ~0u;
+    num_accesses = datasize / 4;
+    if (!(num_accesses <= MAX_ACCESSES_PER_INSN_PER_THREAD)) return ~0u;
+    if (localaddr % 4 != 0) return ~0u;
+    for (unsigned i = 0; i < num_accesses; i++) {
+      address_type local_word = localaddr / 4 + i;
+      translated_addrs[i] = local_word * max_concurrent_threads * 4 + thread_base + LOCAL_GENERIC_START;
+    }
+  } else {
+    if (!(datasize > 0)) return ~0u;
+    num_accesses = 1;
+    address_type local_word = localaddr / 4;
+    address_type local_word_offset = localaddr % 4;
+    if ((localaddr + datasize - 1) / 4 != local_word) return ~0u;
+    translated_addrs[0] = local_word * max_concurrent_threads * 4 + local_word_offset + thread_base + LOCAL_GENERIC_START;
+  }
+  return num_accesses;
+}
+
 int main(int argc, char **argv) {
   if (argc < 3) { fprintf(stderr, "usage: ref_oracle dump|time <traceg> ...\n"); return 2; }
   std::string mode = argv[1];
   const char *trace_path = argv[2];
   const char *out_path = NULL, *cfg_path = NULL;
   int stages = 3;
+  local_map_t lmap = {0, 0, 0, 0, 0};
+  struct local_out_t { uint32_t inst, sid, tid0, n_txn; };
+  std::vector<local_out_t> local_issues;
+  std::vector<ti_txn_rec> local_txn;
   if (mode == "dump") {
     if (argc < 4) return 2;
     out_path = argv[3];
     if (argc > 4) cfg_path = argv[4];
+  } else if (mode == "local") {
+    // ref_oracle local <traceg> <out> <num_shader> <n_thread_per_shader> <local_mem_map> <padded_threads_per_cta> <max_cta_per_shader>
+    // every local load/store is "issued" with the placement block b -> SM b % num_shader, CTA slot (b / num_shader) % max_cta
+    if (argc < 9) return 2;
+    out_path = argv[3];
+    lmap.num_shader = atoi(argv[4]); lmap.n_thread_per_shader = atoi(argv[5]); lmap.local_mem_map = atoi(argv[6]);
+    lmap.padded_threads_per_cta = atoi(argv[7]); lmap.max_cta_per_shader = atoi(argv[8]);
   } else {
     if (argc > 3) cfg_path = argv[3];
     if (argc > 4) stages = !strcmp(argv[4], "parse") ? 1 : !strcmp(argv[4], "convert") ? 2 : 3;
@@ -193,6 +241,44 @@ int main(int argc, char **argv) {
               (inst.op == LOAD_OP || inst.op == STORE_OP) && inst.active_count() > 0)
             cycles = inst.shmem_cycles();
         }
+        if (mode == "local" && is_local && (inst.is_load() || inst.is_store())) {
+          // trace_driven.cc:593-601 (checkExecutionStatusAndUpdate) then trace_driven.cc:620-622
+          const unsigned b = (unsigned)(n_tb_total - 1);
+          local_out_t lo = {(uint32_t)(n_inst_total - 1), b % lmap.num_shader,
+                            ((b / lmap.num_shader) % lmap.max_cta_per_shader) * lmap.padded_threads_per_cta + 32 * w, 0};
+          bool tripped = false;
+          for (unsigned t2 = 0; t2 < 32 && !tripped; ++t2) {
+            if (!inst.active(t2)) continue;
+            new_addr_type localaddrs[MAX_ACCESSES_PER_INSN_PER_THREAD];
+            unsigned num = translate_local_memaddr_restated(lmap, lo.sid, inst.get_addr(t2), lo.tid0 + t2, inst.data_size, localaddrs);
+            if (num == ~0u) { tripped = true; break; }
+            inst.set_addr(t2, (new_addr_type *)localaddrs, num);
+          }
+          if (tripped) lo.n_txn = 0xFFFFFFFFu;
+          else {
+            inst.generate_mem_accesses();
+            std::vector<ti_txn_rec> q;
+            while (!inst.accessq_empty()) {
+              const mem_access_t &a = inst.accessq_back();
+              ti_txn_rec x;
+              memset(&x, 0, sizeof x);
+              x.addr = a.get_addr();
+              x.lane_mask = (uint32_t)a.get_warp_mask().to_ulong();
+              mem_access_byte_mask_t bm = a.get_byte_mask();
+              for (int bb = 0; bb < 128; ++bb)
+                if (bm.test(bb)) x.byte_mask[bb >> 5] |= 1u << (bb & 31);
+              x.size = (uint8_t)a.get_size();
+              x.sector_mask = (uint8_t)a.get_sector_mask().to_ulong();
+              x.type = (uint8_t)a.get_type();
+              x.is_write = a.is_write() ? 1 : 0;
+              q.push_back(x);
+              inst.accessq_pop_back();
+            }
+            lo.n_txn = (uint32_t)q.size();
+            for (size_t k2 = q.size(); k2-- > 0;) local_txn.push_back(q[k2]);
+          }
+          local_issues.push_back(lo);
+        }
         n_txn_total += inst.accessq_count();
         acc.issue(cfg, inst.op, inst.sp_op, inst.active_count(), inst.latency,
                   inst.const_cache_operand, inst.space.get_type(), inst.is_store());
@@ -263,6 +349,17 @@ int main(int argc, char **argv) {
     d.counters = acc.ints;
     d.power = acc.dbl;
     if (!ti_dump_write(d, out_path)) { fprintf(stderr, "cannot write %s\n", out_path); return 3; }
+  }
+  if (mode == "local") {
+    FILE *f = fopen(out_path, "wb");
+    if (!f) { fprintf(stderr, "cannot write %s\n", out_path); return 3; }
+    const uint64_t n = local_issues.size(), nt = local_txn.size();
+    fwrite("TILOCAL1", 1, 8, f);
+    fwrite(&n, 8, 1, f);
+    fwrite(&nt, 8, 1, f);
+    if (n) fwrite(local_issues.data(), sizeof(local_out_t), n, f);
+    if (nt) fwrite(local_txn.data(), sizeof(ti_txn_rec), nt, f);
+    fclose(f);
   }
   printf("{\"impl\":\"reference\",\"stages\":%d,\"seconds\":%.6f,\"n_inst\":%llu,\"n_tb\":%llu,\"n_txn\":%llu}\n",
          stages, sec, (unsigned long long)n_inst_total, (unsigned long long)n_tb_total,

@@ -64,6 +64,19 @@ def regroup_fixtures():
         print("regroup_" + name, len(raw), len(g), out.count("Warning"), "warnings")
 
 
+def local_fixtures():
+    """tests/golden/<trace>.<map>.tilocal: the reference's generate_mem_accesses on every local load / store
+    after translate_local_memaddr with the placement rule of `ref_oracle local`."""
+    import test_local
+    for name, mapname in test_local.FIXTURES:
+        trace, fx = test_local.fixture_paths(name, mapname)
+        r = subprocess.run([REF, "local", trace, fx] + [str(v) for v in test_local.MAPS[mapname]], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        iss, txn = test_local.load_tilocal(fx)
+        print(os.path.basename(fx), len(iss), "issues", len(txn), "transactions")
+
+
 if __name__ == "__main__":
     regroup_fixtures()
+    local_fixtures()
     main()
