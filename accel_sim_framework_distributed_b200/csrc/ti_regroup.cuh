@@ -155,7 +155,8 @@ __global__ void __launch_bounds__(kRgThreads) rg_keys_kernel(const RgParams P) {
         else {
           key = 1u + (uint32_t)(tb * P.warps_per_tb + v4[3]);
           delta = (uint32_t)(q + 1 - ls);
-          atomicMin(&P.tb_first[tb], (uint32_t)ls);
+          // a plain read first: after the block's first few lines the minimum no longer moves (a stale value only costs an atomic)
+          if ((uint32_t)ls < *reinterpret_cast<const volatile uint32_t *>(&P.tb_first[tb])) atomicMin(&P.tb_first[tb], (uint32_t)ls);
         }
       }
       P.start[o] = (uint32_t)ls;
