@@ -274,6 +274,32 @@ def bench_b200(args):
         d2h = 32 * len(view.inst) + 256 * len(view.rows) + 4 * len(view.txn_off) + 32 * len(view.txn) + 32 * len(view.tb) + 16 * len(view.warp)
         torch.cuda.cudart().cudaHostUnregister(pin.data_ptr())
 
+    # ---- what the host link can do on this box (the bound of the end-to-end arm): pinned copies, both directions at once
+    link = None
+    if not args.no_e2e and rank == 0:
+        nb = 1 << 30
+        hp_up, hp_dn = torch.empty(nb, dtype=torch.uint8).pin_memory(), torch.empty(nb, dtype=torch.uint8).pin_memory()
+        d_up, d_dn = torch.empty(nb, dtype=torch.uint8, device="cuda"), torch.empty(nb, dtype=torch.uint8, device="cuda")
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+        best = {}
+        for mode in ("h2d", "d2h", "both"):
+            ts = []
+            for _ in range(3):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                if mode in ("h2d", "both"):
+                    with torch.cuda.stream(s_up):
+                        d_up.copy_(hp_up, non_blocking=True)
+                if mode in ("d2h", "both"):
+                    with torch.cuda.stream(s_dn):
+                        hp_dn.copy_(d_dn, non_blocking=True)
+                torch.cuda.synchronize()
+                ts.append(time.perf_counter() - t0)
+            best[mode] = nb / min(ts) / 1e9
+        link = {"h2d_GB_per_s": best["h2d"], "d2h_GB_per_s": best["d2h"], "each_direction_when_both_GB_per_s": best["both"],
+                "how": "1 GiB pinned <-> device copies, best of 3, wall clock around a synchronize"}
+        del hp_up, hp_dn, d_up, d_dn
+
     # ---- max over ranks
     stats = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device="cuda")
     sums = torch.tensor([float(len(body)), float(counts.n_inst), float(counts.n_txn), float(counts.n_mem)], dtype=torch.float64, device="cuda")
@@ -303,7 +329,8 @@ def bench_b200(args):
                          "frac_of_nominal_8TBs": achieved / 8000.0, "traffic": traffic_bytes(args.workload), "traffic_unit": "dram bytes per launch (ncu, profiles/ncu_traffic.json)", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": b_alg, "kernel": "ti_decode_kernel", "launch_ms": per_launch_ms},
             "e2e": {"value": all_bytes / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": len(body), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_s * 1e3, "warp_insts_per_s": all_inst / e2e_s},
+                    "ms_per_step": e2e_s * 1e3, "warp_insts_per_s": all_inst / e2e_s,
+                    "d2h_GB_per_s_achieved": d2h / e2e_s / 1e9, "host_link": link},
             "gpu_launches": 2 * args.steps,
             "clocks": sampler.summary(),
             "counter_allreduce_ms": allreduce_ms,
