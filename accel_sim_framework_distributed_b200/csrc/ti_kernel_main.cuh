@@ -301,51 +301,52 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     TI_STAMP(5);   // P4 publish (+ early resolve)
     // ---------------------------------------------------------------- P5 structural lines
     // ordinals of "thread block" (low half) and "warp" (high half) lines among the structural lines
-    {
-      ti_tb_rec *tb_out = late ? park_tb : P.tb + ex1[2];
-      ti_warp_rec *warp_out = late ? park_warp : P.warp + ex1[3];
-      const uint64_t tb_room = late ? ~0ull : (P.cap_tb > ex1[2] ? P.cap_tb - ex1[2] : 0);
-      const uint64_t warp_room = late ? ~0ull : (P.cap_warp > ex1[3] ? P.cap_warp - ex1[3] : 0);
-      const uint64_t inst0 = late ? 0 : ex1[0] + P.off_inst, warp0 = late ? 0 : ex1[3] + P.off_warp;
-      block_scan(
-          n_sl, ms->warp_tot,
-          [&](uint32_t i) { const unsigned c = text[sl_off[i]]; return (uint32_t)(c == 't' ? 1u : c == 'w' ? 0x10000u : 0u); },
-          [&](uint32_t i, uint32_t ex, uint32_t) {
-            const int o = sl_off[i];
-            const unsigned c = text[o];
-            // instruction lines before this one = its rank in the sorted inst_off list
-            uint32_t lo = 0, hi = n_inst;
-            while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (inst_off[mid] < o) lo = mid + 1; else hi = mid; }
-            const uint64_t first_inst = inst0 + lo;
-            SlParsed sp = parse_struct_line(text, text32, o);
-            int32_t n = 0;
-            if (sp.type == SL_WARP) {                     // trace_parser.cc:428-437: the next non-blank line must be "insts = n"
-              int q = sp.q;
-              sp.ok = sp.ok && sp.v[0] >= 0;
-              while (text[q] == '\n' && q < 16 + kChunk + kSlack) ++q;
-              sp.ok = sp.ok && load8(text32, (unsigned)q) == kLitInsts0;
-              q += 8;
-              sp.ok = sp.ok && parse_i32(text, q, n) && text[q] == '\n' && n >= 0;
-            }
-            if (sp.type == SL_INSTS) sp.ok = sp.ok && sp.v[0] >= 0;
-            uint32_t fl = sp.ok ? 0u : (uint32_t)TI_EF_BAD_STRUCTURE;
-            if (sp.ok && sp.type != SL_TB && sp.type != SL_WARP)
-              atomicAdd(&cnt[kCntConst + (sp.type == SL_BEGIN ? 1 : sp.type == SL_END ? 2 : 4)], 1u);
-            if (c == 't') {                               // trace_parser.cc:423-427
-              ti_tb_rec r;
-              r.text_off = cb - 16 + (uint64_t)o + (sp.ok ? P.off_text : 0); r.line_len = sp.ok ? (uint32_t)(sp.q - o) : 0u;
-              r.x = sp.ok ? sp.v[0] : 0; r.y = sp.ok ? sp.v[1] : 0; r.z = sp.ok ? sp.v[2] : 0;
-              r.first_warp = sp.ok ? (uint32_t)(warp0 + (ex >> 16)) : 0u; r.first_inst = sp.ok ? (uint32_t)first_inst : 0u;
-              if ((ex & 0xffff) < tb_room) tb_out[ex & 0xffff] = r;
-            } else if (c == 'w') {
-              ti_warp_rec r;  // written even when malformed so the table never holds uninitialised rows
-              r.warp_id = sp.ok ? (uint32_t)sp.v[0] : 0u; r.n_insts = sp.ok ? (uint32_t)n : 0u; r.first_inst = (uint32_t)first_inst; r.reserved = 0;
-              if ((ex >> 16) < warp_room) warp_out[ex >> 16] = r;
-            }
-            if (line_end(nlmap32, (unsigned)o) - (unsigned)o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
-            note_error(ms, fl, tbase + (uint32_t)o);
-          });
-    }
+    ti_tb_rec *tb_out = late ? park_tb : P.tb + ex1[2];
+    ti_warp_rec *warp_out = late ? park_warp : P.warp + ex1[3];
+    const uint64_t tb_room = late ? ~0ull : (P.cap_tb > ex1[2] ? P.cap_tb - ex1[2] : 0);
+    const uint64_t warp_room = late ? ~0ull : (P.cap_warp > ex1[3] ? P.cap_warp - ex1[3] : 0);
+    const uint64_t inst0 = late ? 0 : ex1[0] + P.off_inst, warp0 = late ? 0 : ex1[3] + P.off_warp;
+    auto struct_val = [&](uint32_t i) { const unsigned c = text[sl_off[i]]; return (uint32_t)(c == 't' ? 1u : c == 'w' ? 0x10000u : 0u); };
+    auto struct_line = [&](uint32_t i, uint32_t ex, uint32_t) {
+      const int o = sl_off[i];
+      const unsigned c = text[o];
+      // instruction lines before this one = its rank in the sorted inst_off list
+      uint32_t lo = 0, hi = n_inst;
+      while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (inst_off[mid] < o) lo = mid + 1; else hi = mid; }
+      const uint64_t first_inst = inst0 + lo;
+      SlParsed sp = parse_struct_line(text, text32, o);
+      int32_t n = 0;
+      if (sp.type == SL_WARP) {                     // trace_parser.cc:428-437: the next non-blank line must be "insts = n"
+        int q = sp.q;
+        sp.ok = sp.ok && sp.v[0] >= 0;
+        while (text[q] == '\n' && q < 16 + kChunk + kSlack) ++q;
+        sp.ok = sp.ok && load8(text32, (unsigned)q) == kLitInsts0;
+        q += 8;
+        sp.ok = sp.ok && parse_i32(text, q, n) && text[q] == '\n' && n >= 0;
+      }
+      if (sp.type == SL_INSTS) sp.ok = sp.ok && sp.v[0] >= 0;
+      uint32_t fl = sp.ok ? 0u : (uint32_t)TI_EF_BAD_STRUCTURE;
+      if (sp.ok && sp.type != SL_TB && sp.type != SL_WARP)
+        atomicAdd(&cnt[kCntConst + (sp.type == SL_BEGIN ? 1 : sp.type == SL_END ? 2 : 4)], 1u);
+      if (c == 't') {                               // trace_parser.cc:423-427
+        ti_tb_rec r;
+        r.text_off = cb - 16 + (uint64_t)o + (sp.ok ? P.off_text : 0); r.line_len = sp.ok ? (uint32_t)(sp.q - o) : 0u;
+        r.x = sp.ok ? sp.v[0] : 0; r.y = sp.ok ? sp.v[1] : 0; r.z = sp.ok ? sp.v[2] : 0;
+        r.first_warp = sp.ok ? (uint32_t)(warp0 + (ex >> 16)) : 0u; r.first_inst = sp.ok ? (uint32_t)first_inst : 0u;
+        if ((ex & 0xffff) < tb_room) tb_out[ex & 0xffff] = r;
+      } else if (c == 'w') {
+        ti_warp_rec r;  // written even when malformed so the table never holds uninitialised rows
+        r.warp_id = sp.ok ? (uint32_t)sp.v[0] : 0u; r.n_insts = sp.ok ? (uint32_t)n : 0u; r.first_inst = (uint32_t)first_inst; r.reserved = 0;
+        if ((ex >> 16) < warp_room) warp_out[ex >> 16] = r;
+      }
+      if (line_end(nlmap32, (unsigned)o) - (unsigned)o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
+      note_error(ms, fl, tbase + (uint32_t)o);
+    };
+    // The structural lines are few (tens per chunk) but a long dependent chain: normally the last warp
+    // takes them alone, beside P6a on the other warps (same barrier-delimited phase, below).  Many of
+    // them, or headers that cannot be parked, go CTA-wide here first.
+    const bool p5_beside = kWarps > 1 && late && n_sl <= (uint32_t)kSlSplitMax;
+    if (!p5_beside) block_scan(n_sl, ms->warp_tot, struct_val, struct_line);
 
     TI_STAMP(6);   // P5
     if (pend) {        // the previous chunk's transactions, before P6a reuses the staging area
@@ -357,18 +358,35 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     // Coalesces into the staging area; the address row and the final mem_idx need the prefix and
     // are written in P6c from the descriptor parked here.  The line-offset lists are dead now
     // (P5 has ended with a barrier) and hold the descriptors.
-    StrideNote *notes = reinterpret_cast<StrideNote *>(smem + oInstOff);
-    for (uint32_t fo = tid; fo < n_fast; fo += kThreads) {
+    // Descriptors live in the line-offset lists: behind the entries P5 is still reading when the two
+    // run side by side, over all of both lists when P5 has finished.
+    const uint32_t note_off = p5_beside ? (uint32_t)oSlOff + ((n_sl * 2 + 15) & ~15u) : (uint32_t)oInstOff;
+    StrideNote *notes = reinterpret_cast<StrideNote *>(smem + note_off);
+    const uint32_t note_cap = ((uint32_t)oMemList - note_off) / (uint32_t)sizeof(StrideNote);
+    const uint32_t p6a_threads = p5_beside ? (uint32_t)kThreads - 32u : (uint32_t)kThreads;
+    if (p5_beside && wid == kWarps - 1) {              // P5, one warp: 32 lines per round, ordinals by shuffle scan
+      uint32_t run = 0;
+      for (uint32_t i0 = 0; i0 < n_sl; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const uint32_t v = i < n_sl ? struct_val(i) : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t up = __shfl_up_sync(kFull, inc, d); if ((int)lane >= d) inc += up; }
+        if (i < n_sl) struct_line(i, run + inc - v, v);
+        run += __shfl_sync(kFull, inc, 31);
+      }
+    }
+    for (uint32_t fo = tid; fo < n_fast && tid < p6a_threads; fo += p6a_threads) {
       const uint32_t mo = fast_list[fo];
       ti_inst_rec *rp = recs + mem_list[mo];
       const uint32_t mask = rp->mask, tmp = rp->mem_idx;
       const unsigned ds = rp->data_size, op = rp->op;
       StrideDesc d;
       uint32_t fl = 0;
-      if (fo >= (uint32_t)kNoteCap || !stride_parse(text, tmp & 0xffff, mask, ds ? ds : 1, d, fl)) {
+      if (fo >= note_cap || !stride_parse(text, tmp & 0xffff, mask, ds ? ds : 1, d, fl)) {
         // no room for a descriptor, or the progression wraps around 2^64 (not monotone): warp path
         slow_list[n_slow + atomicAdd(&ms->n_extra, 1u)] = (uint16_t)mo;
-        if (fo < (uint32_t)kNoteCap) notes[fo].flags = kNoteSkip;
+        if (fo < note_cap) notes[fo].flags = kNoteSkip;
         continue;
       }
       const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
@@ -507,7 +525,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       }
     }
     {
-      const uint32_t n_notes = n_fast < (uint32_t)kNoteCap ? n_fast : (uint32_t)kNoteCap;
+      const uint32_t n_notes = n_fast < note_cap ? n_fast : note_cap;
       for (uint32_t fo = tid; fo < n_notes; fo += kThreads) {
         const StrideNote nt = notes[fo];
         if (nt.flags & kNoteSkip) continue;             // went to the warp path, which wrote its row

@@ -72,8 +72,8 @@ static_assert(kTextBytes < 65536, "smem offsets are 16 bit");
 constexpr int kParkMax = 128;                                // staging slots (32 B) lent to parked headers
 struct StrideNote { uint64_t base; int32_t stride; uint32_t flags; };
 constexpr uint32_t kNoteSkip = 1, kNoteEmpty = 2;            // handled by the warp path / no lane carries an address
-constexpr int kNoteCap = (oMemList - oInstOff) / (int)sizeof(StrideNote);
-static_assert(kParkMax < kTxnStage && oInstOff % 16 == 0 && sizeof(StrideNote) == 16, "parking areas");
+constexpr int kSlSplitMax = 96;                              // structural lines one warp handles beside P6a (3 rounds)
+static_assert(kParkMax < kTxnStage && oInstOff % 16 == 0 && oSlOff % 16 == 0 && sizeof(StrideNote) == 16, "parking areas");
 constexpr int kVecPerWarp = ((kChunk / 16 + kWarps - 1) / kWarps + 31) & ~31;  // 16 B vectors of the chunk per warp
 constexpr int kVecIters = kVecPerWarp / 32;
 
