@@ -426,7 +426,8 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
 
     TI_STAMP(8);   // P4' resolve
     // ---------------------------------------------------------------- P6b everything else: warp per instruction
-    for (;;) {
+    // (skipped with its barrier when the chunk has no such instruction: the count is CTA-uniform)
+    if (n_warp_path) for (;;) {
       uint32_t so = 0;
       if (lane == 0) so = atomicAdd(&ms->next_mem, 1u);
       so = __shfl_sync(kFull, so, 0);
@@ -482,7 +483,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         if (pos[1] < n_txn) stage[slot + pos[1]] = reduce_and_send(t2[1], seg, type, is_write);
       }
     }
-    __syncthreads();
+    if (n_warp_path) __syncthreads();
 
     TI_STAMP(9);   // P6b
     // ---------------------------------------------------------------- P7 look-back #2: publish now, resolve in the next iteration
