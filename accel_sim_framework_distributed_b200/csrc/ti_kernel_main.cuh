@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     mbar_init(&ms->mbar[1], 1);
     ms->chunk_next = atomicAdd(&P.g->ticket, 1u);
     if (ms->chunk_next < P.n_chunks) issue_bulk(ms->chunk_next, 0);
+    ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
   }
   __syncthreads();
   if (ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, 0);
@@ -164,10 +165,6 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     const unsigned buf = TI_TEXT_BUFS == 2 ? (iter & 1) : 0u;
     const uint32_t chunk = ms->chunk_next;
     if (chunk >= P.n_chunks) break;
-    if (tid == 0) {
-      ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
-    }
-    __syncthreads();
     uint8_t *text = smem + oText + buf * kTextBytes;
     const uint32_t *text32 = reinterpret_cast<const uint32_t *>(text);
     uint4 *text_v = reinterpret_cast<uint4 *>(text);
@@ -489,8 +486,9 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     // ---------------------------------------------------------------- P7 look-back #2: publish now, resolve in the next iteration
     const uint32_t n_txn_chunk = block_scan(
         n_mem, ms->warp_tot, [&](uint32_t i) { return (uint32_t)txn_cnt[i]; },
-        [&](uint32_t i, uint32_t ex, uint32_t) { txn_loc[i] = (uint16_t)ex; });
+        [&](uint32_t i, uint32_t ex, uint32_t) { txn_loc[i] = (uint16_t)ex; }, false);   // txn_loc is next read after later barriers
     cta_publish2(P.state2, chunk, n_txn_chunk);
+    const uint32_t stage_used = ms->stage_used;        // final since P6b
     // Next ticket + prefetch of that chunk's text into the other buffer (free since the
     // top-of-loop barrier).  Tickets must be taken in the order the chunks really start, or a
     // chunk's predecessor could begin after the chunk itself and every look-back would wait for
@@ -578,7 +576,10 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       atomicMin(&P.g->first_error_off, ms->first_err);
     }
 
-    __syncthreads();   // chunk_next visible
+    __syncthreads();   // chunk_next visible; nobody reads the per-chunk scalars any more
+    if (tid == 0) {    // reset them for the next chunk here: the top-of-loop barrier publishes it
+      ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
+    }
     if (ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, nbuf);
 
     TI_STAMP(12);  // P8
@@ -586,11 +587,11 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     // The staging area, txn_cnt / txn_slot / txn_loc stay untouched until the next chunk's P6a, so
     // resolving look-back #2 can wait until then (half a chunk time of slack).  Not when staging
     // overflowed: the recompute needs this chunk's records.
-    if (ms->stage_used > stage_cap) {
+    if (stage_used > stage_cap) {
       finish_txn(chunk, n_mem, n_txn_chunk, base_mem, true);
     } else {
       pend = true; pend_chunk = chunk; pend_n_mem = n_mem; pend_n_txn = n_txn_chunk; pend_base_mem = base_mem;
-      pend_stage_used = ms->stage_used;
+      pend_stage_used = stage_used;
     }
     TI_STAMP(13);  // P7' (overflow only)
     if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }

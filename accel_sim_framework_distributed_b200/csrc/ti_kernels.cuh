@@ -178,8 +178,8 @@ TI_D void cta_resolve1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64_
         found = true;
       }
     }
-    __syncthreads();   // lb is reused by the next round / the next look-back
-    if (found) break;
+    if (found) break;  // (the next use of lb is behind other barriers)
+    __syncthreads();   // lb is reused by the next round
   }
   if (threadIdx.x == 0) {
     st_vol64(&st[c].inc0, kValid | (excl[1] + agg[1]) << 31 | (excl[0] + agg[0]));
@@ -216,8 +216,8 @@ TI_D uint64_t cta_resolve2(State2 *st, uint32_t c, uint32_t agg, LbWarp *lb) {
       excl += lb[k].s[0];
       if (lb[k].L < 32) { excl += lb[k].i0 & 0x3fffffffffffffffull; found = true; }
     }
-    __syncthreads();
     if (found) break;
+    __syncthreads();
   }
   if (threadIdx.x == 0) st_vol64(&st[c].w, kValid | (excl + agg));
   return excl;
@@ -238,9 +238,10 @@ TI_D uint32_t nl_mask16(const uint4 x) {
 }
 
 // Exclusive scan of small per-item values over items [0, n), in item order, by the
-// whole CTA (two ballot-free passes, one barrier).  val(i) is evaluated twice.
+// whole CTA (two ballot-free passes, one barrier between them, one after unless the caller's
+// next reader of emit()'s output sits behind another barrier anyway).  val(i) is evaluated twice.
 template <class V, class E>
-TI_D uint32_t block_scan(uint32_t n, uint64_t *warp_tot, V val, E emit) {
+TI_D uint32_t block_scan(uint32_t n, uint64_t *warp_tot, V val, E emit, bool sync_after = true) {
   const unsigned lane = lane_id(), w = threadIdx.x >> 5;
   const uint32_t seg = ((n + kWarps - 1) / kWarps + 31) & ~31u;
   const uint32_t lo = w * seg, hi = lo + seg < n ? lo + seg : n;
@@ -263,7 +264,7 @@ TI_D uint32_t block_scan(uint32_t n, uint64_t *warp_tot, V val, E emit) {
     if (i < hi) emit(i, base + inc - v, v);
     base += __shfl_sync(kFull, inc, 31);
   }
-  __syncthreads();
+  if (sync_after) __syncthreads();   // what emit() wrote is visible to the whole CTA
   return total;
 }
 
