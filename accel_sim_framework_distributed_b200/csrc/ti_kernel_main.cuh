@@ -186,40 +186,47 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         cls_masks16(text_v[v], nl16, dl16);
         nlmap[v] = (uint16_t)nl16; dlmap[v] = (uint16_t)dl16;
       }
-    uint32_t starts[kVecIters];
-    uint32_t excl[kVecIters];
-    uint32_t run = 0;
+    // Each lane takes kVecIters CONSECUTIVE 16 B vectors (48 B apart from its neighbours': the 16 B
+    // loads stay bank-conflict free), so that its line starts are contiguous in file order and one
+    // shuffle scan per warp orders them all.
+    uint32_t starts[kVecIters], m[kVecIters];
+    const uint32_t v0 = wid * kVecPerWarp + lane * kVecIters;
 #pragma unroll
-    for (int it = 0; it < kVecIters; ++it) {
-      const uint32_t v = wid * kVecPerWarp + it * 32 + lane, s0 = v * 16;
-      const bool inside = v < (uint32_t)(kChunk / 16);
-      uint32_t m = 0, dl16 = 0;
-      if (inside) {
-        cls_masks16(text_v[1 + v], m, dl16);
-        nlmap[1 + v] = (uint16_t)m; dlmap[1 + v] = (uint16_t)dl16;
+    for (int j = 0; j < kVecIters; ++j) {
+      const uint32_t v = v0 + j;
+      uint32_t dl16 = 0;
+      m[j] = 0;
+      if (v < (uint32_t)(kChunk / 16)) {
+        cls_masks16(text_v[1 + v], m[j], dl16);
+        nlmap[1 + v] = (uint16_t)m[j]; dlmap[1 + v] = (uint16_t)dl16;
       }
-      const uint32_t up = __shfl_up_sync(kFull, m, 1);
-      const uint32_t prev = lane ? (up >> 15) & 1 : (inside && text[16 + s0 - 1] == '\n');
-      uint32_t st = ((m << 1) | prev) & ~m & 0xffffu;
+    }
+    const uint32_t up = __shfl_up_sync(kFull, m[kVecIters - 1], 1);
+    uint32_t packed = 0;
+#pragma unroll
+    for (int j = 0; j < kVecIters; ++j) {
+      const uint32_t v = v0 + j, s0 = v * 16;
+      const bool inside = v < (uint32_t)(kChunk / 16);
+      const uint32_t prev = j ? (m[j ? j - 1 : 0] >> 15) & 1 : lane ? (up >> 15) & 1 : (uint32_t)(inside && text[16 + s0 - 1] == '\n');
+      uint32_t st = ((m[j] << 1) | prev) & ~m[j] & 0xffffu;
       if (!inside || s0 >= lim) st = 0;
       else if (s0 + 16 > lim) st &= (1u << (lim - s0)) - 1;
-      uint32_t packed = 0;
       for (uint32_t b = st; b; b &= b - 1) {
         const unsigned c = text[16 + s0 + __ffs(b) - 1];
-        if (hexval(c) < 16) packed += 1u;
+        if (hexval(c) < 16) { packed += 1u; st |= (b & (0u - b)) << 16; }   // high half: which starts are instruction lines
         else {
           packed += 1u << 16;
           if (c == 't') atomicAdd(&ms->n_tb, 1u);
           if (c == 'w') atomicAdd(&ms->n_warp, 1u);
         }
       }
-      uint32_t inc = packed;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) { const uint32_t u = __shfl_up_sync(kFull, inc, d); if ((int)lane >= d) inc += u; }
-      starts[it] = st;
-      excl[it] = run + inc - packed;
-      run += __shfl_sync(kFull, inc, 31);
+      starts[j] = st;
     }
+    uint32_t inc = packed;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t u = __shfl_up_sync(kFull, inc, d); if ((int)lane >= d) inc += u; }
+    const uint32_t excl = inc - packed;
+    const uint32_t run = __shfl_sync(kFull, inc, 31);
     if (lane == 0) ms->warp_tot[wid] = run;
     __syncthreads();
     uint32_t pbase = 0, ptot = 0;
@@ -230,13 +237,13 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       if (tid == 0) note_error(ms, TI_EF_DENSE_CHUNK, (uint32_t)cb);
       n_inst = n_sl = n_tb = n_warp = 0;
     } else {
+      uint32_t at = pbase + excl;
 #pragma unroll
-      for (int it = 0; it < kVecIters; ++it) {
-        const uint32_t s0 = (wid * kVecPerWarp + it * 32 + lane) * 16;
-        uint32_t at = pbase + excl[it];
-        for (uint32_t b = starts[it]; b; b &= b - 1) {
+      for (int j = 0; j < kVecIters; ++j) {
+        const uint32_t s0 = (v0 + j) * 16;
+        for (uint32_t b = starts[j] & 0xffffu; b; b &= b - 1) {
           const uint32_t o = 16 + s0 + __ffs(b) - 1;
-          if (hexval(text[o]) < 16) { inst_off[at & 0xffff] = (uint16_t)o; at += 1; }
+          if ((starts[j] >> 16) & b & (0u - b)) { inst_off[at & 0xffff] = (uint16_t)o; at += 1; }
           else { sl_off[at >> 16] = (uint16_t)o; at += 1u << 16; }
         }
       }
