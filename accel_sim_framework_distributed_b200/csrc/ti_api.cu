@@ -326,8 +326,8 @@ ti_status ti_kernel_sync(ti_kernel *k, ti_counts *counts) {
   uint32_t ef = g->error_flags;
   if (hc->n_begin_tb != hc->n_end_tb || hc->n_begin_tb != hc->n_tb || hc->reserved[0] != hc->n_warp) ef |= TI_EF_BAD_STRUCTURE;
   k->counts.error_flags = ef;
-  k->counts.first_error_line_off = g->first_error_off;
-  k->synced = true;
+  k->counts.first_error_line_off = g->first_error_off == 0xffffffffu ? 0 : g->first_error_off;
+  k->synced = ef == 0;   // a shard with grammar errors has counts and flags, but nothing to fetch
   if (counts) *counts = k->counts;
   if (ef) { ti::set_error("trace text outside the tracer grammar: flags 0x%x near shard offset %u", ef, g->first_error_off); return TI_ERR_PARSE; }
   return TI_OK;
@@ -456,6 +456,7 @@ static ti_status launch_decode(ti_kernel *k) {
   CK(cudaMemsetAsync(k->state1.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s));
   CK(cudaMemsetAsync(k->state2.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s));
   CK(cudaMemsetAsync(k->globals.p, 0, sizeof(ti::Globals), s));
+  CK(cudaMemsetAsync(&((ti::Globals *)k->globals.p)->first_error_off, 0xff, 4, s));   // atomicMin target
   CK(cudaMemsetAsync(k->counters.p, 0, sizeof(ti_counters), s));
   CK(cudaMemsetAsync(k->txn_off.p, 0, 4, s));
   if (n_chunks) {
@@ -629,6 +630,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     CK(cudaMemsetAsync(t.state1.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s_c));
     CK(cudaMemsetAsync(t.state2.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s_c));
     CK(cudaMemsetAsync(t.globals.p, 0, sizeof(ti::Globals), s_c));
+    CK(cudaMemsetAsync(&((ti::Globals *)t.globals.p)->first_error_off, 0xff, 4, s_c));
     CK(cudaMemsetAsync(t.counters.p, 0, sizeof(ti_counters), s_c));
     CK(cudaMemsetAsync(t.txn_off.p, 0, 4, s_c));
     if (n_chunks) {
@@ -815,6 +817,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
   CK(cudaMemsetAsync(P.state1, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s));
   CK(cudaMemsetAsync(P.state2, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s));
   CK(cudaMemsetAsync(io->d_status, 0, sizeof(ti::Globals), s));
+  CK(cudaMemsetAsync(&((ti::Globals *)io->d_status)->first_error_off, 0xff, 4, s));
   CK(cudaMemsetAsync(io->d_counters, 0, sizeof(ti_counters), s));
   CK(cudaMemsetAsync(io->d_txn_off, 0, 4, s));
   if (n_chunks) {

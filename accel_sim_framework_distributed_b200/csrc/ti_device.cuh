@@ -103,7 +103,7 @@ struct State1 { unsigned long long agg, inc0, inc1, pad; };
 struct State2 { unsigned long long w; };
 constexpr unsigned long long kValid = 1ull << 63, kAggValid = 1ull << 62;
 
-struct Globals {        // zeroed before launch
+struct Globals {        // zeroed before launch (first_error_off: all ones)
   uint32_t ticket;      // next chunk to hand out
   uint32_t error_flags; // TI_EF_*
   uint32_t first_error_off;

@@ -80,6 +80,13 @@ def run_error(tp, tmp_path, name):
     tp.kernel_finalizer(k)
     assert st == _ffi.TI_ERR_PARSE, (name, st)
     assert counts.error_flags & _ffi.EF[flag], (name, hex(counts.error_flags))
+    # the reported offset lies inside the offending line (the second instruction line of these images)
+    body = img[k.hdr.body_offset:]
+    first = b"0000 ffffffff 1 R1 FADD 2 R2 R3 0 0\n"
+    if flag not in ("BAD_STRUCTURE", "FRAMING", "UNDEF_SPACE") and first in body:
+        lo = body.index(first) + len(first)
+        hi = body.index(b"\n", lo)
+        assert lo <= counts.first_error_line_off < hi, (name, counts.first_error_line_off, lo, hi)
     # the restatement raises the same flag
     assert harness.oracle_flags(path, str(tmp_path)) & _ffi.EF[flag], name
 
