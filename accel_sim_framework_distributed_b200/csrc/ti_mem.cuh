@@ -366,17 +366,25 @@ TI_D_COLD unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_
       const uint32_t g = __match_any_sync(mA, keyA);
       leadA = (unsigned)(__ffs(g) - 1) == lane;
       ta.block = keyA; ta.lanes = g;
+      ta.bytes[0] = wa[0]; ta.bytes[1] = wa[1]; ta.bytes[2] = wa[2]; ta.bytes[3] = wa[3]; ta.chunks = ca;
+      // a redux with a partial mask issues once per distinct mask: a fully divergent access would
+      // run it 32 times with one lane each, so lanes alone in their block skip it
+      if (g & (g - 1)) {
 #pragma unroll
-      for (int w = 0; w < 4; ++w) ta.bytes[w] = __reduce_or_sync(g, wa[w]);
-      ta.chunks = __reduce_or_sync(g, ca);
+        for (int w = 0; w < 4; ++w) ta.bytes[w] = __reduce_or_sync(g, wa[w]);
+        ta.chunks = __reduce_or_sync(g, ca);
+      }
     }
     if (stradp) {
       const uint32_t g = __match_any_sync(mB, keyB);
       leadB = (unsigned)(__ffs(g) - 1) == lane;
       tb.block = keyB; tb.lanes = g;
+      tb.bytes[0] = wb[0]; tb.bytes[1] = wb[1]; tb.bytes[2] = wb[2]; tb.bytes[3] = wb[3]; tb.chunks = cb;
+      if (g & (g - 1)) {
 #pragma unroll
-      for (int w = 0; w < 4; ++w) tb.bytes[w] = __reduce_or_sync(g, wb[w]);
-      tb.chunks = __reduce_or_sync(g, cb);
+        for (int w = 0; w < 4; ++w) tb.bytes[w] = __reduce_or_sync(g, wb[w]);
+        tb.chunks = __reduce_or_sync(g, cb);
+      }
     }
     const uint32_t LA = __ballot_sync(kFull, leadA);
     unsigned cntA = 0, cntB = 0;

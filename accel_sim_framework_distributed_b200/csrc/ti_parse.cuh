@@ -33,8 +33,9 @@
 
 namespace ti {
 
-TI_HD bool is_ws(unsigned c) { return c == ' ' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
-TI_HD bool is_end(unsigned c) { return c == '\n' || is_ws(c); }
+// blank = ' ' or 0x09..0x0d without '\n' (what operator>> skips inside a line); end = blank or '\n'
+TI_HD bool is_end(unsigned c) { return c == ' ' || c - 9u <= 4u; }
+TI_HD bool is_ws(unsigned c) { return is_end(c) && c != '\n'; }
 TI_HD unsigned hexval(unsigned c) {  // 0..15, or >= 16 when not a hex digit
   unsigned d = c - '0';
   if (d <= 9) return d;
