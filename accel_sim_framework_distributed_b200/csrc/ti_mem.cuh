@@ -12,6 +12,10 @@
 #include "ti_device.cuh"
 #include "ti_parse.cuh"
 
+#ifndef TI_SWAR_ADDR
+#define TI_SWAR_ADDR 1
+#endif
+
 namespace ti {
 
 constexpr unsigned kFull = 0xffffffffu;
@@ -124,7 +128,15 @@ TI_D_COLD uint64_t decode_addresses(const uint8_t *text, unsigned q, unsigned mo
   if (active && rank < ntok) {
     Reader rd = {text, (int)tokpos[rank]};
     bool ok;
-    if (mode == 0 || rank == 0) ok = rd.hex(16, val);
+    const uint32_t *t32 = reinterpret_cast<const uint32_t *>(text);
+    const unsigned tp = tokpos[rank];
+    // the tracer writes every address as 0x%016lx: 18 characters, converted four digits at a time
+    uint32_t h0, h1, h2, h3;
+    if (TI_SWAR_ADDR && (mode == 0 || rank == 0) && text[tp] == '0' && (text[tp + 1] | 0x20) == 'x' && is_end(text[tp + 18]) &&
+        hex4(load4(t32, tp + 2), 4, h0) & hex4(load4(t32, tp + 6), 4, h1) & hex4(load4(t32, tp + 10), 4, h2) & hex4(load4(t32, tp + 14), 4, h3)) {
+      val = (uint64_t)h0 << 48 | (uint64_t)h1 << 32 | (uint64_t)h2 << 16 | h3;
+      ok = true;
+    } else if (mode == 0 || rank == 0) ok = rd.hex(16, val);
     else { int64_t d; ok = rd.sdec(0x7fffffffffffffffull, d); val = (uint64_t)d; }
     if (!ok) flags |= TI_EF_BAD_NUMBER;
   }
@@ -389,9 +401,15 @@ TI_D_COLD unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_
     const uint32_t LA = __ballot_sync(kFull, leadA);
     unsigned cntA = 0, cntB = 0;
     int owner = -1;
-    for (uint32_t m = LA; m; m &= m - 1) {               // broadcast every A-leader's block once
+    // every leader's block goes through the warp's scratch once: a broadcast LDS.64 per leader instead
+    // of two shuffles (a divergent access has 32 leaders)
+    uint64_t *ks = reinterpret_cast<uint64_t *>(scratch);
+    __syncwarp();
+    ks[lane] = keyA;
+    __syncwarp();
+    for (uint32_t m = LA; m; m &= m - 1) {
       const int j = __ffs(m) - 1;
-      const uint64_t kj = __shfl_sync(kFull, keyA, j);
+      const uint64_t kj = ks[j];
       cntA += kj < keyA;
       cntB += kj < keyB;
       if (leadB && kj == keyB) owner = j;
@@ -400,12 +418,16 @@ TI_D_COLD unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_
     if (mB) {                                            // warp-uniform
       const bool pureB = leadB && owner < 0, owned = leadB && owner >= 0;
       LBp = __ballot_sync(kFull, pureB);
+      __syncwarp();
+      ks[lane] = keyB;
+      __syncwarp();
       for (uint32_t m = LBp; m; m &= m - 1) {
         const int j = __ffs(m) - 1;
-        const uint64_t kj = __shfl_sync(kFull, keyB, j);
+        const uint64_t kj = ks[j];
         cntA += kj < keyA;
         cntB += kj < keyB;
       }
+      __syncwarp();                                      // the scratch is reused for the merge slots below
       const uint32_t ownedmask = __reduce_or_sync(kFull, owned ? 1u << owner : 0u);
       if (ownedmask) {
         if (owned) {
