@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       const unsigned ds = rp->data_size, pack_b = rp->pack_b;
       __syncwarp();
       uint32_t fl = 0;
-      const uint64_t addr = decode_addresses(text, tmp & 0xffff, mode, mask, tokpos, fl);
+      const uint64_t addr = decode_addresses(text, dlmap32, tmp & 0xffff, line_end(nlmap32, tmp & 0xffff), mode, mask, tokpos, fl);
       fl = __reduce_or_sync(kFull, fl);              // a bad token is seen by one lane only: make it warp-uniform
       const uint64_t row = base_mem + mo;
       if (row < P.cap_mem) P.rows[row * 32 + lane] = addr;

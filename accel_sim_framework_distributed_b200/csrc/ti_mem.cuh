@@ -80,10 +80,10 @@ TI_D ti_txn_rec reduce_and_send(const Txn &t, unsigned seg, unsigned type, unsig
   return r;
 }
 
-// ---- address decompression.  `q` = smem offset of the first token after the mode
-// field; tokpos = 33 u16 of per-warp scratch.  Returns this lane's address.
-TI_D_COLD uint64_t decode_addresses(const uint8_t *text, unsigned q, unsigned mode, uint32_t mask, uint16_t *tokpos,
-                               uint32_t &flags) {
+// ---- address decompression.  `q` = smem offset of the first token after the mode field, `le` =
+// offset of the line's '\n'; tokpos = 33 u16 of per-warp scratch.  Returns this lane's address.
+TI_D_COLD uint64_t decode_addresses(const uint8_t *text, const uint32_t *dlmap32, unsigned q, unsigned le, unsigned mode, uint32_t mask,
+                               uint16_t *tokpos, uint32_t &flags) {
   const unsigned lane = lane_id();
   const bool active = mask >> lane & 1;
   if (mode == 1) {  // every lane reads the same two tokens (smem broadcast)
@@ -104,24 +104,34 @@ TI_D_COLD uint64_t decode_addresses(const uint8_t *text, unsigned q, unsigned mo
     return base + (uint64_t)stride * (uint64_t)(lane - first);
   }
   if (mode != 0 && mode != 2) return 0;             // value-initialised addresses stay 0
-  // ---- list / delta: token k belongs to the k-th active lane
+  // ---- list / delta: token k belongs to the k-th active lane.  Token starts come from the
+  // delimiter bitmap P1 built: lane l owns bitmap word (q >> 5) + l, i.e. 32 characters, so a
+  // 650-character list-mode line is one round (a ballot per 32 characters took twenty).
   const unsigned nact = __popc(mask);
   const unsigned rank = __popc(mask & lanemask_lt());
+  const unsigned wq = q >> 5, wle = le >> 5;
   unsigned ntok = 0;
-  unsigned prev_ws = 1;                              // q follows a delimiter
-  for (unsigned base = q;; base += 32) {
-    const unsigned c = text[base + lane];
-    const unsigned nlb = __ballot_sync(kFull, c == '\n');
-    unsigned wsb = __ballot_sync(kFull, is_end(c));
-    const unsigned valid = nlb ? ((1u << (__ffs(nlb) - 1)) - 1) : kFull;  // bytes before the newline
-    const unsigned start = ~wsb & (wsb << 1 | prev_ws) & valid;
-    if (start >> lane & 1) {
-      const unsigned k = ntok + __popc(start & lanemask_lt());
-      if (k < 33) tokpos[k] = (uint16_t)(base + lane);
-    }
-    ntok += __popc(start);
-    prev_ws = wsb >> 31;
-    if (nlb || ntok >= nact) break;
+  uint32_t carry = 1;                                // the character before q is a delimiter
+  for (unsigned wb = wq;; wb += 32) {
+    const unsigned w = wb + lane;
+    const uint32_t dl = dlmap32[w < wle ? w : wle];
+    uint32_t valid = w > wle ? 0u : kFull;
+    if (w == wq) valid &= ~0u << (q & 31);
+    if (w == wle) valid &= (1u << (le & 31)) - 1;
+    const uint32_t up = __shfl_up_sync(kFull, dl, 1);
+    uint32_t before = (dl << 1) | (lane ? up >> 31 : carry);     // bit b = character b-1 is a delimiter
+    if (w == wq) before |= 1u << (q & 31);
+    const uint32_t start = ~dl & before & valid;
+    const unsigned cnt = __popc(start);
+    unsigned inc = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const unsigned u = __shfl_up_sync(kFull, inc, d); if ((int)lane >= d) inc += u; }
+    unsigned k = ntok + inc - cnt;
+    for (uint32_t b = start; b; b &= b - 1, ++k)
+      if (k < 33) tokpos[k] = (uint16_t)((w << 5) + __ffs(b) - 1);
+    ntok += __shfl_sync(kFull, inc, 31);
+    carry = __shfl_sync(kFull, dl, 31) >> 31;
+    if (wb + 32 > wle || ntok >= nact) break;        // warp-uniform
   }
   __syncwarp();
   uint64_t val = 0;
