@@ -417,12 +417,16 @@ TI_D_COLD unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_
     __syncwarp();
     ks[lane] = keyA;
     __syncwarp();
-    for (uint32_t m = LA; m; m &= m - 1) {
-      const int j = __ffs(m) - 1;
-      const uint64_t kj = ks[j];
-      cntA += kj < keyA;
-      cntB += kj < keyB;
-      if (leadB && kj == keyB) owner = j;
+    if (!mB) {                                           // warp-uniform: nobody straddles, only A ranks are needed
+      for (uint32_t m = LA; m; m &= m - 1) cntA += ks[__ffs(m) - 1] < keyA;
+    } else {
+      for (uint32_t m = LA; m; m &= m - 1) {
+        const int j = __ffs(m) - 1;
+        const uint64_t kj = ks[j];
+        cntA += kj < keyA;
+        cntB += kj < keyB;
+        if (leadB && kj == keyB) owner = j;
+      }
     }
     uint32_t LBp = 0;
     if (mB) {                                            // warp-uniform
