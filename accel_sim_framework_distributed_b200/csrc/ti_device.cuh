@@ -53,6 +53,9 @@ namespace ti {
 #ifndef TI_TEXT_BUFS
 #define TI_TEXT_BUFS 1     // text buffers; the text is dead after P6b, so one buffer takes the prefetch of the next chunk too
 #endif
+#ifndef TI_TMA_STORE
+#define TI_TMA_STORE 1     // P8: the chunk's record block leaves shared memory as one TMA bulk store
+#endif
 #ifndef TI_MIN_BLOCKS
 #define TI_MIN_BLOCKS 3   // resident CTAs per SM the register allocation is bounded for
 #endif

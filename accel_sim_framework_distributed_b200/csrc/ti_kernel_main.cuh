@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
   if (ms->chunk_next < P.n_chunks) fill_edges(ms->chunk_next, 0);
 
   for (unsigned iter = 0;; ++iter) {
+    if (tid == 0) bulk_store_wait_read();   // the previous chunk's record block has left shared memory
     __syncthreads();  // previous chunk fully drained; edge fills of this chunk's buffer visible
     const unsigned buf = TI_TEXT_BUFS == 2 ? (iter & 1) : 0u;
     const uint32_t chunk = ms->chunk_next;
@@ -556,10 +557,14 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
 
     TI_STAMP(11);  // P6c
     // ---------------------------------------------------------------- P8 records out + counters
-    {
+    // The record block is contiguous in smem and in HBM: one TMA bulk store by one thread (below, after
+    // the barrier) once every record's mem_idx has been made file-global in place.  Only a block that
+    // would run past the output capacity is copied by the threads, record by record.
+    const uint32_t mem0 = (uint32_t)(base_mem + P.off_mem);
+    const bool recs_bulk = TI_TMA_STORE && base_inst + n_inst <= P.cap_inst;
+    if (!recs_bulk) {
       const uint4 *src = reinterpret_cast<const uint4 *>(recs);
       uint4 *dst = reinterpret_cast<uint4 *>(P.inst + base_inst);
-      const uint32_t mem0 = (uint32_t)(base_mem + P.off_mem);
       for (uint32_t k = tid; k < 2 * n_inst; k += kThreads) {
         uint4 v = src[k];
         if (!(k & 1) && v.w != 0xFFFFFFFFu) v.w += mem0;   // mem_idx: chunk-relative ordinal -> file-global row
@@ -567,7 +572,8 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       }
     }
     for (uint32_t io = tid; io < n_inst; io += kThreads) {
-      const ti_inst_rec *rp = recs + io;
+      ti_inst_rec *rp = recs + io;
+      if (recs_bulk && rp->mem_idx != 0xFFFFFFFFu) rp->mem_idx += mem0;
       const unsigned op = rp->op, sp = rp->pack_a & 0x1f, act = __popc(rp->mask);
       atomicAdd(&cnt[kCntHist + sp * 33 + act], 1u);
       atomicAdd(&cnt[kCntOp + fold_op(op)], 1u);
@@ -583,7 +589,11 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       atomicMin(&P.g->first_error_off, ms->first_err);
     }
 
-    __syncthreads();   // chunk_next visible; nobody reads the per-chunk scalars any more
+    __syncthreads();   // chunk_next visible; nobody reads the per-chunk scalars any more; records final
+    if (tid == 0 && recs_bulk && n_inst) {
+      fence_proxy_async();                             // the records were written through the generic proxy
+      bulk_s2g(P.inst + base_inst, recs, n_inst * (unsigned)sizeof(ti_inst_rec));
+    }
     if (tid == 0) {    // reset them for the next chunk here: the top-of-loop barrier publishes it
       ms->next_mem = 0; ms->stage_used = 0; ms->err = 0; ms->first_err = 0xffffffffu; ms->n_tb = 0; ms->n_warp = 0; ms->n_extra = 0;
     }
@@ -604,6 +614,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }
   }
   if (pend) finish_txn(pend_chunk, pend_n_mem, pend_n_txn, pend_base_mem, false);
+  if (tid == 0) bulk_store_wait_all();
   __syncthreads();
   flush_counters(cnt, P.counters);
 }

@@ -86,6 +86,9 @@ TI_D void mbar_expect_tx(uint64_t *, unsigned) {}
 TI_D void bulk_g2s(void *dst, const void *src, unsigned bytes, uint64_t *) { memcpy(dst, src, bytes); }
 TI_D void mbar_wait(uint64_t *, unsigned) {}
 TI_D void fence_proxy_async() {}
+TI_D void bulk_s2g(void *dst, const void *src, unsigned bytes) { memcpy(dst, src, bytes); }
+TI_D void bulk_store_wait_read() {}
+TI_D void bulk_store_wait_all() {}
 #else
 TI_D uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 TI_D void mbar_init(uint64_t *b, unsigned count) {
@@ -109,6 +112,13 @@ TI_D void mbar_wait(uint64_t *b, unsigned parity) {
                  : "memory");
 }
 TI_D void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// shared -> global bulk copy (TMA store, SASS UBLKCP.S2G); completion tracked by the thread's bulk group
+TI_D void bulk_s2g(void *dst, const void *src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+TI_D void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }   // the source may be overwritten
+TI_D void bulk_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }          // the writes have been performed
 #endif
 
 
