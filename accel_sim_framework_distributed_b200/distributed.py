@@ -54,6 +54,33 @@ def allreduce_counters(counters, device=None, group=None):
     return np.frombuffer(t.cpu().numpy().tobytes(), dtype=R.COUNTERS)[0]
 
 
+def exchange_offsets(counts, device=None, group=None):
+    """Level-2 sharding: every rank decoded one byte range of the same kernel file and holds
+    shard-relative record indices.  All-gathers the five per-rank totals (n_inst, n_mem, n_txn,
+    n_tb, n_warp -- 40 bytes per rank, the only other exchange of the path) and returns this
+    rank's bases: adding them to first_inst / first_warp / mem_idx / txn_off gives the file-global
+    ordinals, i.e. the reference's file-order thread-block hand-out across GPUs."""
+    import torch
+    import torch.distributed as dist
+
+    names = ("n_inst", "n_mem", "n_txn", "n_tb", "n_warp")
+    mine = torch.tensor([int(getattr(counts, n) if hasattr(counts, n) else counts[n]) for n in names], dtype=torch.int64)
+    if device is not None:
+        mine = mine.to(device)
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    rank = dist.get_rank(group) if world > 1 else 0
+    if world > 1:
+        parts = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine, group=group)
+        allc = torch.stack(parts).cpu().numpy()
+    else:
+        allc = mine.cpu().numpy()[None, :]
+    base = allc[:rank].sum(axis=0) if rank else np.zeros(len(names), dtype=np.int64)
+    out = {n[2:]: int(b) for n, b in zip(names, base)}
+    out["totals"] = {n[2:]: int(t) for n, t in zip(names, allc.sum(axis=0))}
+    return out
+
+
 def finalize(parser, counters):
     """ti_counters_finalize through a trace_parser: integer block -> AccelWattch doubles."""
     cnt = np.zeros(1, dtype=R.COUNTERS)

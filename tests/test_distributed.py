@@ -54,6 +54,13 @@ def _worker(rank, world, port, mode, paths, out_dir):
             assert b == 0 or b == e or bytes(body[b:b + 9]) == b"#BEGIN_TB"
             d = k.run(b, e)
             acc[0] = d.counters
+            # global ordinals: shard-relative first_inst / first_warp + this rank's bases
+            base = D.exchange_offsets(d.counts)
+            tb = d.tb.copy()
+            tb["first_inst"] += np.uint32(base["inst"]); tb["first_warp"] += np.uint32(base["warp"])
+            np.save(os.path.join(out_dir, "tb%d.npy" % rank), tb)
+            np.save(os.path.join(out_dir, "base%d.npy" % rank), np.array([base["inst"], base["mem"], base["txn"], base["tb"], base["warp"],
+                                                                         base["totals"]["inst"], base["totals"]["tb"]], dtype=np.int64))
             tp.kernel_finalizer(k)
         total = D.allreduce_counters(acc[0])
         power = D.finalize(tp, total)
@@ -127,6 +134,14 @@ def test_gloo_sharded_by_byte_range(tmp_path):
     want, dumps = _oracle_sum([p], tmp)
     _check(cnt, pw, want, dumps[0].power)
     assert int(own[0]["n_inst"]) > 0 and int(own[1]["n_inst"]) > 0
+    # exchange_offsets: rank 1's bases are rank 0's totals, and the shifted thread-block table is the whole file's
+    b0, b1 = (np.load(os.path.join(tmp, "base%d.npy" % r)) for r in range(WORLD))
+    assert not b0[:5].any() and b1[0] == int(own[0]["n_inst"]) and b1[3] == int(own[0]["n_tb"]) and b1[5] == int(cnt[0]["n_inst"])
+    tb = np.concatenate([np.load(os.path.join(tmp, "tb%d.npy" % r)) for r in range(WORLD)])
+    whole = dumps[0].tb
+    assert len(tb) == len(whole) == b1[6]
+    for f in ("x", "y", "z", "first_warp", "first_inst"):
+        assert np.array_equal(tb[f], whole[f]), f
 
 
 def test_rank_assignment_helpers():
