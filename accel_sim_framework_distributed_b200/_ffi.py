@@ -81,6 +81,10 @@ class LocalMap(C.Structure):
 TI_LOCAL_GENERIC_START = 0xC0000000 - 80 * (96 << 10) - 80 * 2048 * (1 << 14)
 
 
+class DerivedStats(C.Structure):
+    _fields_ = [("active_lane_distro", C.c_uint64 * 33), ("smem_bank_conflict", C.c_uint64), ("uncoalesced_gmem", C.c_uint64)]
+
+
 class RegroupStats(C.Structure):
     _fields_ = [("n_lines", C.c_uint64), ("n_keys", C.c_uint64), ("out_bytes", C.c_uint64), ("n_tb_written", C.c_uint32),
                 ("n_tb_empty", C.c_uint32), ("n_warp_empty", C.c_uint32), ("device_ms", C.c_float)]
@@ -97,7 +101,7 @@ SYMBOLS = [
     "ti_kernel_close", "ti_kernel_upload", "ti_kernel_decode", "ti_kernel_sync", "ti_kernel_fetch",
     "ti_kernel_dev_view", "ti_kernel_counters", "ti_counters_add", "ti_counters_finalize", "ti_kernel_timing",
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
-    "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local",
+    "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local", "ti_counters_derive",
 ]
 
 
@@ -147,6 +151,7 @@ def load_library(path=None):
         "ti_regroup_commandlist": (C.c_int, [C.c_char_p, S, C.c_char_p, S, P(S)]),
         "ti_regroup_buckets": (C.c_int, [V, P(V), P(V), P(U64), P(C.c_uint32)]),
         "ti_kernel_coalesce_local": (C.c_int, [V, P(LocalMap), V, S, V, S, V, P(S)]),
+        "ti_counters_derive": (C.c_int, [V, P(DerivedStats)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -165,5 +170,5 @@ def np_view(ptr, dtype, n, shape=None):
     return a.reshape(shape) if shape else a
 
 
-__all__ = ["load_library", "NoAllocIO", "RegroupStats", "LocalMap", "TI_LOCAL_GENERIC_START", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "DevView", "Command", "TraceIngestError", "np_view",
+__all__ = ["load_library", "NoAllocIO", "RegroupStats", "DerivedStats", "LocalMap", "TI_LOCAL_GENERIC_START", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "DevView", "Command", "TraceIngestError", "np_view",
            "SYMBOLS", "EF", "R"]

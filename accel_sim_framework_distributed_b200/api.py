@@ -272,6 +272,14 @@ class trace_parser:  # noqa: N801 -- the reference's class name (trace_parser.h:
         self._ck(self.lib.ti_regroup_commandlist(text, len(text), out, n.value, C.byref(n)))
         return out.raw[:n.value]
 
+    def derive(self, counters):
+        """ti_counters_derive: the trace-derivable statistics of SURVEY 8 f3 from a counter block."""
+        cnt = np.zeros(1, dtype=R.COUNTERS)
+        cnt[0] = counters
+        out = _ffi.DerivedStats()
+        self._ck(self.lib.ti_counters_derive(cnt.ctypes.data, C.byref(out)))
+        return out
+
     def plan_shards(self, body, n):
         body = np.ascontiguousarray(body, dtype=np.uint8)
         cuts = (C.c_size_t * (n + 1))()

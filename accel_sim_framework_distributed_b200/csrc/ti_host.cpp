@@ -258,3 +258,14 @@ extern "C" ti_status ti_regroup_commandlist(const char *text, size_t len, char *
   if (need > cap || (!out && need)) { ti::set_error("kernelslist.g needs %zu bytes", need); return TI_ERR_CAPACITY; }
   return TI_OK;
 }
+
+// the statistics that are functions of the counter block
+extern "C" ti_status ti_counters_derive(const ti_counters *c, ti_derived_stats *out) {
+  if (!c || !out) return TI_ERR_INVALID_ARG;
+  memset(out, 0, sizeof *out);
+  for (int sp = 0; sp < TI_N_SP_OPS; ++sp)
+    for (int a = 0; a <= 32; ++a) out->active_lane_distro[a] += c->hist[sp][a];   // shader.cc:1045, one count per issued warp instruction
+  out->smem_bank_conflict = c->smem_cycles;   // abstract_hardware_model.cc:415-418: cycles = total_accesses, reported as is
+  out->uncoalesced_gmem = c->n_txn;           // abstract_hardware_model.cc:467-470: every access pushed for a global instruction
+  return TI_OK;
+}

@@ -24,11 +24,18 @@ def parser_with(tp, over):
     return trace_parser(lib_path=lib_path, config=T.qv100_config(**over)), True
 
 
-def check_against_dump(d, o, offsets, skip_counters=("reserved", "n_begin_tb", "n_end_tb", "text_bytes", "n_warp", "n_mem")):
+def check_against_dump(d, o, offsets, skip_counters=("reserved", "n_begin_tb", "n_end_tb", "text_bytes", "n_warp", "n_mem"), tp=None):
     msgs = T.compare(d, o, offsets=offsets, text_a=d.text, names=("cuda", "oracle"))
     msgs += T.compare_counters(d.counters, o.counters, skip=skip_counters)
     msgs += T.compare_power(d.power, o.power, rtol=POWER_RTOL)
     assert not msgs, "\n".join(msgs[:12])
+    # when the dump comes from the reference-built oracle it carries what the reference's OWN
+    # ptx_file_line_stats_add_smem_bank_conflict / _uncoalesced_gmem calls added up to
+    if tp is not None and int(o.counters["reserved"][3]) == 1:
+        ds = tp.derive(d.counters)
+        assert ds.smem_bank_conflict == int(o.counters["reserved"][1])
+        assert ds.uncoalesced_gmem == int(o.counters["reserved"][2])
+        assert list(ds.active_lane_distro) == [int(v) for v in np.asarray(o.counters["hist"]).sum(axis=0)]
 
 
 def golden_names():
@@ -43,7 +50,7 @@ def run_golden(tp, name):
         k = p.parse_kernel_info(os.path.join(GOLDEN, name + ".traceg"))
         d = k.run()
         o = T.load_dump(os.path.join(GOLDEN, name + ".tidump"))
-        check_against_dump(d, o, offsets=False)
+        check_against_dump(d, o, offsets=False, tp=p)
         p.kernel_finalizer(k)
     finally:
         if own:
@@ -60,7 +67,7 @@ def run_generated(tp, tmp_path, over=None, **gen):
         d = k.run()
         cfg = T.qv100_config(**over) if over else None
         o = T.load_dump(harness.oracle_dump(path, str(tmp_path), config=cfg))
-        check_against_dump(d, o, offsets=harness.oracle_kind() == "port")
+        check_against_dump(d, o, offsets=harness.oracle_kind() == "port", tp=p)
         p.kernel_finalizer(k)
         return d
     finally:
