@@ -226,7 +226,7 @@ TI_D bool stride_is_dense(const StrideDesc &d, unsigned ds) {
 }
 TI_D unsigned dense_count(const StrideDesc &d, unsigned ds, unsigned seg) {
   const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)d.n * ds;
-  return (unsigned)((((end - 1) & segmask) - (d.base & segmask)) / seg) + 1;
+  return (unsigned)((((end - 1) & segmask) - (d.base & segmask)) >> (__ffs(seg) - 1)) + 1;   // seg is 32, 64 or 128: no 64-bit division
 }
 TI_D unsigned dense_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out) {
   const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)d.n * ds;
