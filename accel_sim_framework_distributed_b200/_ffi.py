@@ -101,7 +101,7 @@ SYMBOLS = [
     "ti_kernel_close", "ti_kernel_upload", "ti_kernel_decode", "ti_kernel_sync", "ti_kernel_fetch",
     "ti_kernel_dev_view", "ti_kernel_counters", "ti_counters_add", "ti_counters_finalize", "ti_kernel_timing",
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
-    "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local", "ti_counters_derive",
+    "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local", "ti_counters_derive", "ti_kernel_path_stats",
 ]
 
 
@@ -152,6 +152,7 @@ def load_library(path=None):
         "ti_regroup_buckets": (C.c_int, [V, P(V), P(V), P(U64), P(C.c_uint32)]),
         "ti_kernel_coalesce_local": (C.c_int, [V, P(LocalMap), V, S, V, S, V, P(S)]),
         "ti_counters_derive": (C.c_int, [V, P(DerivedStats)]),
+        "ti_kernel_path_stats": (C.c_int, [V, P(C.c_uint32 * 4)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

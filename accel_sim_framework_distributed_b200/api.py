@@ -96,6 +96,12 @@ class KernelTrace:
         self._p._ck(self._p.lib.ti_kernel_dev_view(self._h, C.byref(v)))
         return v
 
+    def path_stats(self):
+        """(staging overflows, early resolves, parking clashes, descriptor-list overflows) of the last decode."""
+        out = (C.c_uint32 * 4)()
+        self._p._ck(self._p.lib.ti_kernel_path_stats(self._h, C.byref(out)))
+        return tuple(out)
+
     def decode_ms(self):
         ms = C.c_float()
         self._p._ck(self._p.lib.ti_kernel_timing(self._h, C.byref(ms)))

@@ -393,6 +393,14 @@ ti_status ti_counters_finalize(const ti_ctx *ctx, const ti_counters *c, ti_power
   return ti_counters_finalize_cfg(&ctx->cfg, c, out);
 }
 
+ti_status ti_kernel_path_stats(ti_kernel *k, uint32_t out[4]) {
+  if (!k || !out) return TI_ERR_INVALID_ARG;
+  if (!k->decoded || k->streamed || !k->h_small.p) return TI_ERR_STATE;
+  const ti::Globals *g = (const ti::Globals *)k->h_small.p;   // brought to the host by ti_kernel_sync
+  for (int i = 0; i < 4; ++i) out[i] = g->rare[i];
+  return TI_OK;
+}
+
 ti_status ti_kernel_timing(ti_kernel *k, float *decode_ms) {
   if (!k || !decode_ms) return TI_ERR_INVALID_ARG;
   if (!k->synced) return TI_ERR_STATE;

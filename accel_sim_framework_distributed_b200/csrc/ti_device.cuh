@@ -111,7 +111,8 @@ struct Globals {        // zeroed before launch (first_error_off: all ones)
   uint32_t error_flags; // TI_EF_*
   uint32_t first_error_off;
   uint32_t overflow;    // bit0 inst, bit1 mem, bit2 txn, bit3 tb, bit4 warp capacity exceeded
-  uint32_t pad[4];
+  uint32_t rare[4];     // how often the rare paths ran: [0] staging overflow (recompute), [1] headers not parked (early
+                        // resolve), [2] previous chunk's records reached into the parking area, [3] descriptor list full
 };
 
 struct DecodeParams {

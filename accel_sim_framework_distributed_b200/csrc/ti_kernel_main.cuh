@@ -298,7 +298,9 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     ti_warp_rec *park_warp = reinterpret_cast<ti_warp_rec *>(stage + stage_cap + n_tb);
     uint64_t ex1[4] = {0, 0, 0, 0};
     if (!late) cta_resolve1(P.state1, chunk, agg1, ex1, ms->lb);
+    if (tid == 0 && !late) atomicAdd(&P.g->rare[1], 1u);
     if (pend && late && pend_stage_used > stage_cap) {   // the previous chunk's staged records reach into this chunk's parking area
+      if (tid == 0) atomicAdd(&P.g->rare[2], 1u);
       finish_txn(pend_chunk, pend_n_mem, pend_n_txn, pend_base_mem, false);
       pend = false;
     }
@@ -391,7 +393,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       if (fo >= note_cap || !stride_parse(text, tmp & 0xffff, mask, ds ? ds : 1, d, fl)) {
         // no room for a descriptor, or the progression wraps around 2^64 (not monotone): warp path
         slow_list[n_slow + atomicAdd(&ms->n_extra, 1u)] = (uint16_t)mo;
-        if (fo < note_cap) notes[fo].flags = kNoteSkip;
+        if (fo < note_cap) notes[fo].flags = kNoteSkip; else atomicAdd(&P.g->rare[3], 1u);
         continue;
       }
       const unsigned seg = segment_size(P, ds, rp->pack_c >> 4 & 7);
@@ -605,6 +607,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     // resolving look-back #2 can wait until then (half a chunk time of slack).  Not when staging
     // overflowed: the recompute needs this chunk's records.
     if (stage_used > stage_cap) {
+      if (tid == 0) atomicAdd(&P.g->rare[0], 1u);
       finish_txn(chunk, n_mem, n_txn_chunk, base_mem, true);
     } else {
       pend = true; pend_chunk = chunk; pend_n_mem = n_mem; pend_n_txn = n_txn_chunk; pend_base_mem = base_mem;

@@ -165,3 +165,51 @@ def run_streamed(tp, tmp_path, shard_bytes, **gen):
     for n, w in want.items():
         assert np.array_equal(getattr(d, n), w), n
     tp.kernel_finalizer(k)
+
+
+def run_rare_paths(tp, tmp_path, n_units=20):
+    """The kernel's rare per-chunk paths really run (ti_kernel_path_stats) and give oracle-identical
+    results: staging overflow + recompute, headers that cannot be parked (early look-back resolve),
+    and a previous chunk whose staged records reach into the next chunk's parking area."""
+    tmp = str(tmp_path)
+
+    def decode(img, name):
+        path = os.path.join(tmp, name + ".traceg")
+        open(path, "wb").write(img)
+        k = tp.parse_kernel_info(path)
+        d = k.run()
+        stats = k.path_stats()
+        o = T.load_dump(harness.oracle_dump(path, tmp, name=name + ".tidump"))
+        check_against_dump(d, o, offsets=harness.oracle_kind() == "port", tp=tp)
+        tp.kernel_finalizer(k)
+        return stats
+
+    # [0] more transactions in a chunk than the staging area holds
+    lines = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (16 * i, 0x7F0000000000 + 4096 * i) for i in range(150)]
+    assert decode(edge_cases.image([(b, 0, 0, [lines, lines]) for b in range(2)]), "overflow")[0] > 0
+    # [1] more thread-block / warp headers in a chunk than the parking area holds
+    assert decode(edge_cases.VALID["edge_many_headers"][0], "headers")[1] > 0
+    # [2] the SAME CTA decodes a chunk that fills the staging area almost to the brim and then a chunk with many
+    # headers to park.  Units of exactly one chunk (12 KiB, padded with blank lines), four brim-full ones for
+    # every header-rich one, more units than resident CTAs so that every CTA sees several.
+    chunk = 12288
+    mem = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (16 * i, 0x7F0000000000 + 4096 * i) for i in range(18)]
+    mem += ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 4 0" % (0x1000 + 16 * i, 0x7F2000000000 + 128 * i) for i in range(13)]   # 18*32 + 13*4 = 628
+    pad = ["%04x ffffffff 1 R1 FADD 2 R2 R3 0 0" % (0x4000 + 16 * i) for i in range(200)]
+    img0 = edge_cases.image([])
+    head = img0[:tp.parse_header(np.frombuffer(img0, dtype=np.uint8)[:8192].copy()).body_offset]
+
+    def unit(tbs):
+        text = edge_cases.image(tbs)[len(head):].rstrip(b"\n") + b"\n"
+        assert len(text) <= chunk
+        return text + b"\n" * (chunk - len(text))
+
+    body, b = [], 0
+    for u in range(n_units):
+        if u % 5 == 4:
+            body.append(unit([(b + j, 0, 0, [["0000 ffffffff 1 R1 FADD 2 R2 R3 0 0"], []]) for j in range(16)]))
+            b += 16
+        else:
+            body.append(unit([(b, 0, 0, [mem + pad, []])]))
+            b += 1
+    assert decode(head + b"".join(body), "clash")[2] > 0

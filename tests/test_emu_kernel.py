@@ -52,3 +52,7 @@ def test_emu_staging_overflow_and_capacity_retry(emu_parser, tmp_path):
 
 def test_emu_streamed(emu_parser, tmp_path):
     parity_cases.run_streamed(emu_parser, tmp_path, 40000, profile=5, seed=21, n_tb=24, insts_per_warp=8, block_threads=96)
+
+
+def test_emu_rare_paths(emu_parser, tmp_path):
+    parity_cases.run_rare_paths(emu_parser, tmp_path)

@@ -147,3 +147,7 @@ def test_full_size_properties(cuda_parser):
 @pytest.mark.parametrize("shard_bytes", [1 << 20, 300000])
 def test_streamed_host_path(cuda_parser, tmp_path, shard_bytes):
     parity_cases.run_streamed(cuda_parser, tmp_path, shard_bytes, profile=5, seed=31, n_tb=800, insts_per_warp=10, block_threads=128)
+
+
+def test_rare_paths(cuda_parser, tmp_path):
+    parity_cases.run_rare_paths(cuda_parser, tmp_path, n_units=2000)   # more chunks than resident CTAs (444)
