@@ -189,6 +189,9 @@ def run_rare_paths(tp, tmp_path, n_units=20):
     assert decode(edge_cases.image([(b, 0, 0, [lines, lines]) for b in range(2)]), "overflow")[0] > 0
     # [1] more thread-block / warp headers in a chunk than the parking area holds
     assert decode(edge_cases.VALID["edge_many_headers"][0], "headers")[1] > 0
+    # [3] more base+stride instructions in a chunk than descriptors fit beside the structural-line list
+    lines = ["%04x 00000001 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 4 0" % (16 * i, 0x7F3000000000 + 256 * i) for i in range(700)]
+    assert decode(edge_cases.image([(0, 0, 0, [lines, []])]), "notes_full")[3] > 0
     # [2] the SAME CTA decodes a chunk that fills the staging area almost to the brim and then a chunk with many
     # headers to park.  Units of exactly one chunk (12 KiB, padded with blank lines), four brim-full ones for
     # every header-rich one, more units than resident CTAs so that every CTA sees several.
