@@ -64,6 +64,11 @@ struct HostBuf {
   void release() { if (p) cudaFreeHost(p); p = nullptr; bytes = 0; }
 };
 
+// the four look-back chains of a launch live back to back in one scratch buffer
+void set_chains(ti::DecodeParams &P, void *base, uint32_t n_chunks) {
+  for (int i = 0; i < ti::kChains; ++i) P.chain[i] = (unsigned long long *)base + (size_t)i * (n_chunks + 1);
+}
+
 int arch_column(unsigned v) {  // trace_driven.cc:100-118
   switch (v) {
     case 35: return 0;
@@ -106,7 +111,7 @@ struct ti_kernel {
   DevBuf d_text;
   size_t sh_begin = 0, sh_len = 0;
   bool uploaded = false, decoded = false, synced = false, retried = false;
-  DevBuf inst, rows, txn_off, txn, tb, warp, state1, state2, globals, counters;
+  DevBuf inst, rows, txn_off, txn, tb, warp, chains, globals, counters;
   uint64_t cap_inst = 0, cap_mem = 0, cap_txn = 0, cap_tb = 0, cap_warp = 0;
   HostBuf h_inst, h_rows, h_txn_off, h_txn, h_tb, h_warp, h_small;
   ti_counts counts;
@@ -124,10 +129,12 @@ int ti_device_count(void) {
   return n;
 }
 
+static ti_status ctx_init(ti_ctx *c, const ti_config *cfg);
+
 ti_status ti_ctx_create(const ti_config *cfg, ti_ctx **out) {
   if (!cfg || !out) return TI_ERR_INVALID_ARG;
   *out = nullptr;
-  if (ti_device_count() <= cfg->device) { ti::set_error("CUDA device %d not present", cfg->device); return TI_ERR_NO_DEVICE; }
+  if (cfg->device < 0 || ti_device_count() <= cfg->device) { ti::set_error("CUDA device %d not present", cfg->device); return TI_ERR_NO_DEVICE; }
   if (cfg->coalesce_arch < 13) { ti::set_error("coalesce_arch < 13 aborts in the reference (abstract_hardware_model.cc:436)"); return TI_ERR_INVALID_ARG; }
   const int parts = cfg->mem_warp_parts;
   if (parts < 1 || parts > 32 || (32 % parts) || cfg->num_shmem_bank < 1) { ti::set_error("bad mem_warp_parts / num_shmem_bank"); return TI_ERR_INVALID_ARG; }
@@ -138,6 +145,13 @@ ti_status ti_ctx_create(const ti_config *cfg, ti_ctx **out) {
   }
   ti_ctx *c = new ti_ctx;
   c->cfg = *cfg;
+  const ti_status st = ctx_init(c, cfg);
+  if (st != TI_OK) { ti_ctx_destroy(c); return st; }   // nothing half-built is left behind
+  *out = c;
+  return TI_OK;
+}
+
+static ti_status ctx_init(ti_ctx *c, const ti_config *cfg) {
   CK(cudaSetDevice(cfg->device));
   CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&c->ev0));
@@ -176,7 +190,6 @@ ti_status ti_ctx_create(const ti_config *cfg, ti_ctx **out) {
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ti::ti_decode_kernel, ti::kThreads, ti::kSmemBytes));
   if (per_sm < 1) { ti::set_error("decode kernel does not fit on an SM"); return TI_ERR_CUDA; }
   c->grid = sms * per_sm;
-  *out = c;
   return TI_OK;
 }
 
@@ -208,6 +221,7 @@ static ti_status new_kernel(ti_ctx *ctx, const ti_kernel_hdr *hdr, ti_kernel **o
 
 ti_status ti_kernel_open_file(ti_ctx *ctx, const char *path, ti_kernel_hdr *hdr, ti_kernel **out) {
   if (!ctx || !path || !out) return TI_ERR_INVALID_ARG;
+  CK(cudaSetDevice(ctx->cfg.device));
   FILE *f = fopen(path, "rb");
   if (!f) { ti::set_error("Unable to open file: %s", path); return TI_ERR_IO; }  // trace_parser.cc:306-309
   fseek(f, 0, SEEK_END);
@@ -253,7 +267,7 @@ void ti_kernel_close(ti_kernel *k) {
   if (!k) return;
   cudaStreamSynchronize(k->ctx->stream);
   stream_state_free(k->streams);
-  DevBuf *d[] = {&k->d_text, &k->inst, &k->rows, &k->txn_off, &k->txn, &k->tb, &k->warp, &k->state1, &k->state2, &k->globals, &k->counters};
+  DevBuf *d[] = {&k->d_text, &k->inst, &k->rows, &k->txn_off, &k->txn, &k->tb, &k->warp, &k->chains, &k->globals, &k->counters};
   for (DevBuf *b : d) b->release();
   HostBuf *h[] = {&k->h_file, &k->h_inst, &k->h_rows, &k->h_txn_off, &k->h_txn, &k->h_tb, &k->h_warp, &k->h_small};
   for (HostBuf *b : h) b->release();
@@ -263,6 +277,7 @@ void ti_kernel_close(ti_kernel *k) {
 ti_status ti_kernel_upload(ti_kernel *k, size_t begin, size_t end) {
   if (k && end == (size_t)-1) end = k->body_len;
   if (!k || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
+  CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
   if (end - begin > 0xfffffff0ull) { ti::set_error("shard of %zu bytes: cut it with ti_plan_shards", end - begin); return TI_ERR_TOO_LARGE; }
   k->decoded = k->synced = k->retried = k->streamed = false;
   if (k->d_borrowed) {
@@ -280,6 +295,7 @@ ti_status ti_kernel_upload(ti_kernel *k, size_t begin, size_t end) {
 ti_status ti_kernel_decode(ti_kernel *k) {
   if (!k) return TI_ERR_INVALID_ARG;
   if (!k->uploaded) { ti::set_error("ti_kernel_decode before ti_kernel_upload"); return TI_ERR_STATE; }
+  CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
   const ti_config &cfg = k->ctx->cfg;
   const double len = (double)k->sh_len;
   // default capacities: the instruction bound is exact (no tracer line is shorter than 24
@@ -298,6 +314,7 @@ ti_status ti_kernel_decode(ti_kernel *k) {
 ti_status ti_kernel_sync(ti_kernel *k, ti_counts *counts) {
   if (!k) return TI_ERR_INVALID_ARG;
   if (!k->decoded) { ti::set_error("ti_kernel_sync before ti_kernel_decode"); return TI_ERR_STATE; }
+  CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
   ti_ctx *c = k->ctx;
   ti_status st = k->h_small.ensure(sizeof(ti::Globals) + sizeof(ti_counters));
   if (st != TI_OK) return st;
@@ -336,6 +353,7 @@ ti_status ti_kernel_sync(ti_kernel *k, ti_counts *counts) {
 ti_status ti_kernel_fetch(ti_kernel *k, ti_view *v) {
   if (!k || !v) return TI_ERR_INVALID_ARG;
   if (!k->synced) { ti::set_error("ti_kernel_fetch before a successful ti_kernel_sync"); return TI_ERR_STATE; }
+  CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
   if (k->streamed) {  // ti_kernel_decode_streamed already brought everything to the host
     v->text = k->h_body;
     v->inst = (const ti_inst_rec *)k->h_inst.p; v->addr_rows = (const uint64_t *)k->h_rows.p;
@@ -374,6 +392,7 @@ ti_status ti_kernel_fetch(ti_kernel *k, ti_view *v) {
 ti_status ti_kernel_dev_view(ti_kernel *k, ti_dev_view *v) {
   if (!k || !v) return TI_ERR_INVALID_ARG;
   if (!k->synced) { ti::set_error("ti_kernel_dev_view before a successful ti_kernel_sync"); return TI_ERR_STATE; }
+  if (k->streamed) { ti::set_error("ti_kernel_dev_view after ti_kernel_decode_streamed: the results are on the host (ti_kernel_fetch)"); return TI_ERR_STATE; }
   v->text = k->d_borrowed ? (const void *)(k->d_borrowed + k->sh_begin) : k->d_text.p;
   v->inst = k->inst.p; v->addr_rows = k->rows.p; v->txn_off = k->txn_off.p; v->txn = k->txn.p;
   v->tb = k->tb.p; v->warp = k->warp.p; v->counters = k->counters.p;
@@ -422,8 +441,7 @@ static ti_status launch_decode(ti_kernel *k) {
   if ((st = k->txn.ensure(k->cap_txn * sizeof(ti_txn_rec))) != TI_OK) return st;
   if ((st = k->tb.ensure(k->cap_tb * sizeof(ti_tb_rec))) != TI_OK) return st;
   if ((st = k->warp.ensure(k->cap_warp * sizeof(ti_warp_rec))) != TI_OK) return st;
-  if ((st = k->state1.ensure((size_t)(n_chunks + 1) * sizeof(ti::State1))) != TI_OK) return st;
-  if ((st = k->state2.ensure((size_t)(n_chunks + 1) * sizeof(ti::State2))) != TI_OK) return st;
+  if ((st = k->chains.ensure(ti::chain_bytes(n_chunks))) != TI_OK) return st;
   if ((st = k->globals.ensure(sizeof(ti::Globals))) != TI_OK) return st;
   if ((st = k->counters.ensure(sizeof(ti_counters))) != TI_OK) return st;
 
@@ -440,7 +458,7 @@ static ti_status launch_decode(ti_kernel *k) {
   P.txn = (ti_txn_rec *)k->txn.p; P.cap_txn = k->cap_txn;
   P.tb = (ti_tb_rec *)k->tb.p; P.cap_tb = k->cap_tb;
   P.warp = (ti_warp_rec *)k->warp.p; P.cap_warp = k->cap_warp;
-  P.state1 = (ti::State1 *)k->state1.p; P.state2 = (ti::State2 *)k->state2.p;
+  set_chains(P, k->chains.p, n_chunks);
   P.g = (ti::Globals *)k->globals.p;
   P.counters = (unsigned long long *)k->counters.p;
   P.isa = c->d_isa[k->col]; P.spop = c->d_spop;
@@ -461,8 +479,7 @@ static ti_status launch_decode(ti_kernel *k) {
   P.shmem_limited_broadcast = cfg.shmem_limited_broadcast; P.gmem_skip_L1D = cfg.gmem_skip_L1D;
 
   CK(cudaEventRecord(c->ev0, s));
-  CK(cudaMemsetAsync(k->state1.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s));
-  CK(cudaMemsetAsync(k->state2.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s));
+  CK(cudaMemsetAsync(k->chains.p, 0, ti::chain_bytes(n_chunks), s));
   CK(cudaMemsetAsync(k->globals.p, 0, sizeof(ti::Globals), s));
   CK(cudaMemsetAsync(&((ti::Globals *)k->globals.p)->first_error_off, 0xff, 4, s));   // atomicMin target
   CK(cudaMemsetAsync(k->counters.p, 0, sizeof(ti_counters), s));
@@ -498,7 +515,7 @@ static ti_status launch_decode(ti_kernel *k) {
 namespace {
 
 struct StreamSet {
-  DevBuf text, inst, rows, txn_off, txn, tb, warp, state1, state2, globals, counters;
+  DevBuf text, inst, rows, txn_off, txn, tb, warp, chains, globals, counters;
   HostBuf small;                           // Globals + ti_counters of the shard
   cudaEvent_t ev_h2d = nullptr, ev_dec = nullptr, ev_d2h = nullptr, t0 = nullptr, t1 = nullptr;
 };
@@ -538,7 +555,7 @@ struct ti_stream_state : StreamState {};
 static void stream_state_free(ti_stream_state *ss) {
   if (!ss) return;
   for (StreamSet &t : ss->set) {
-    DevBuf *d[] = {&t.text, &t.inst, &t.rows, &t.txn_off, &t.txn, &t.tb, &t.warp, &t.state1, &t.state2, &t.globals, &t.counters};
+    DevBuf *d[] = {&t.text, &t.inst, &t.rows, &t.txn_off, &t.txn, &t.tb, &t.warp, &t.chains, &t.globals, &t.counters};
     for (DevBuf *b : d) b->release();
     t.small.release();
     cudaEvent_t *e[] = {&t.ev_h2d, &t.ev_dec, &t.ev_d2h, &t.t0, &t.t1};
@@ -553,13 +570,25 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
   if (!k || !v) return TI_ERR_INVALID_ARG;
   if (!k->h_body && k->body_len) { ti::set_error("ti_kernel_decode_streamed needs a host-resident body"); return TI_ERR_STATE; }
   if (k->body_len > 0xfffffff0ull) { ti::set_error("body of %zu bytes: opcode offsets are 32 bit", k->body_len); return TI_ERR_TOO_LARGE; }
+  CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
   ti_ctx *c = k->ctx;
   const ti_config &cfg = c->cfg;
   if (!shard_bytes) shard_bytes = (size_t)64 << 20;
-  const int n_sh = (int)std::max<size_t>(1, (k->body_len + shard_bytes - 1) / shard_bytes);
+  int n_sh = (int)std::max<size_t>(1, (k->body_len + shard_bytes - 1) / shard_bytes);
   std::vector<size_t> cuts(n_sh + 1);
   ti_status st = ti_plan_shards(k->h_body, k->body_len, n_sh, cuts.data());
   if (st != TI_OK) return st;
+  // ti_plan_shards returns empty tail shards when no "#BEGIN_TB" lies behind a nominal cut (a thread block longer
+  // than a shard, fewer thread blocks than shards).  An empty shard launches nothing, so its buffers would hand
+  // stale values (the CSR sentinel txn_off[0]) to the copies below: drop them here.
+  {
+    int m = 0;
+    for (int i = 0; i < n_sh; ++i)
+      if (cuts[i + 1] > cuts[i]) cuts[++m] = cuts[i + 1];
+    if (!m) { m = 1; cuts[1] = k->body_len; }               // an empty body stays one (empty) shard
+    n_sh = m;
+    cuts.resize(m + 1);
+  }
   size_t max_len = 0;
   for (int i = 0; i < n_sh; ++i) max_len = std::max(max_len, cuts[i + 1] - cuts[i]);
 
@@ -589,8 +618,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     if ((st = t.txn.ensure(cap_txn * sizeof(ti_txn_rec))) != TI_OK) return st;
     if ((st = t.tb.ensure(cap_tb * sizeof(ti_tb_rec))) != TI_OK) return st;
     if ((st = t.warp.ensure(cap_warp * sizeof(ti_warp_rec))) != TI_OK) return st;
-    if ((st = t.state1.ensure((size_t)(max_chunks + 1) * sizeof(ti::State1))) != TI_OK) return st;
-    if ((st = t.state2.ensure((size_t)(max_chunks + 1) * sizeof(ti::State2))) != TI_OK) return st;
+    if ((st = t.chains.ensure(ti::chain_bytes(max_chunks))) != TI_OK) return st;
     if ((st = t.globals.ensure(sizeof(ti::Globals))) != TI_OK) return st;
     if ((st = t.counters.ensure(sizeof(ti_counters))) != TI_OK) return st;
     if ((st = t.small.ensure(sizeof(ti::Globals) + sizeof(ti_counters))) != TI_OK) return st;
@@ -628,15 +656,14 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     P.txn = (ti_txn_rec *)t.txn.p; P.cap_txn = cap_txn;
     P.tb = (ti_tb_rec *)t.tb.p; P.cap_tb = cap_tb;
     P.warp = (ti_warp_rec *)t.warp.p; P.cap_warp = cap_warp;
-    P.state1 = (ti::State1 *)t.state1.p; P.state2 = (ti::State2 *)t.state2.p;
+    set_chains(P, t.chains.p, n_chunks);
     P.g = (ti::Globals *)t.globals.p; P.counters = (unsigned long long *)t.counters.p;
     P.off_inst = T_inst; P.off_mem = T_mem; P.off_txn = T_txn; P.off_warp = T_warp; P.off_text = cuts[i];
 
     CK(cudaStreamWaitEvent(s_c, t.ev_h2d, 0));
     if (i >= 2) CK(cudaStreamWaitEvent(s_c, t.ev_d2h, 0));    // D2H(i-2) has drained this set's outputs
     CK(cudaEventRecord(t.t0, s_c));
-    CK(cudaMemsetAsync(t.state1.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s_c));
-    CK(cudaMemsetAsync(t.state2.p, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s_c));
+    CK(cudaMemsetAsync(t.chains.p, 0, ti::chain_bytes(n_chunks), s_c));
     CK(cudaMemsetAsync(t.globals.p, 0, sizeof(ti::Globals), s_c));
     CK(cudaMemsetAsync(&((ti::Globals *)t.globals.p)->first_error_off, 0xff, 4, s_c));
     CK(cudaMemsetAsync(t.counters.p, 0, sizeof(ti_counters), s_c));
@@ -665,7 +692,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     ms_sum += ms;
     if (g->overflow) { overflow = true; break; }
     flags |= g->error_flags;
-    if (g->error_flags && g->first_error_off < first_err) first_err = g->first_error_off + (uint32_t)cuts[i];
+    if (g->error_flags && first_err == 0xffffffffu) first_err = g->first_error_off + (uint32_t)cuts[i];   // shards come in file order: the first one wins
     // host arrays: grow when the running totals no longer fit (first shard: extrapolate)
     const double scale = 1.15 * (double)k->body_len / (double)std::max<size_t>(1, cuts[i + 1]);
     struct { HostBuf *b; uint64_t have, add; size_t elt; } need[] = {
@@ -720,7 +747,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
   k->counts.first_error_line_off = first_err == 0xffffffffu ? 0 : first_err;
   k->sh_begin = 0; k->sh_len = k->body_len;
   k->decode_ms = ms_sum;
-  k->synced = true; k->decoded = true; k->streamed = true;
+  k->synced = flags == 0; k->decoded = true; k->streamed = true;   // as ti_kernel_sync: nothing to fetch after a grammar error
   if (flags) { ti::set_error("trace text outside the tracer grammar: flags 0x%x near body offset %u", flags, k->counts.first_error_line_off); return TI_ERR_PARSE; }
   v->text = k->h_body;
   v->inst = (const ti_inst_rec *)k->h_inst.p;
@@ -737,10 +764,10 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
 // ti_decode_noalloc: the same fused decode, for callers that cannot let the library
 // allocate (see include/traceingest.h).  It has no counterpart in the reference.
 //
-// The only memory the decode needs beyond its inputs and outputs is the pair of
+// The only memory the decode needs beyond its inputs and outputs is the set of
 // per-chunk look-back tables.  For this entry point they live in the file-scope device
 // array below instead of a cudaMalloc'ed buffer: (TI_NOALLOC_MAX_TEXT / chunk + 2)
-// entries of 32 + 8 bytes, about 0.9 MB, resident on every GPU that loads the library
+// entries of 32 bytes, about 0.7 MB, resident on every GPU that loads the library
 // for as long as the process lives.
 //
 // In host code the name `g_noalloc_scratch` is only a handle for the symbol, not an
@@ -754,7 +781,9 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
 // =====================================================================================
 namespace {
 constexpr size_t kNoallocChunks = (size_t)(TI_NOALLOC_MAX_TEXT / ti::kChunk) + 2;
-constexpr size_t kNoallocBytes = kNoallocChunks * (sizeof(ti::State1) + sizeof(ti::State2));
+constexpr size_t kNoallocBytes = ti::chain_bytes(kNoallocChunks - 1);
+static_assert(ti::kChunk != 12288 || kNoallocBytes == TI_NOALLOC_SCRATCH_BYTES,  // (tuning builds use other chunk sizes)
+              "TI_NOALLOC_SCRATCH_BYTES in traceingest.h must state the real size of the scratch array");
 constexpr int kMaxDevices = 64;
 void *g_noalloc_addr[kMaxDevices];  // device address of the array, per device ordinal (0 = not looked up yet)
 }  // namespace
@@ -800,8 +829,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
   P.txn = (ti_txn_rec *)io->d_txn; P.cap_txn = io->cap_txn;
   P.tb = (ti_tb_rec *)io->d_tb; P.cap_tb = io->cap_tb;
   P.warp = (ti_warp_rec *)io->d_warp; P.cap_warp = io->cap_warp;
-  P.state1 = (ti::State1 *)scratch;
-  P.state2 = (ti::State2 *)(scratch + kNoallocChunks * sizeof(ti::State1));
+  set_chains(P, scratch, n_chunks);
   P.g = (ti::Globals *)io->d_status;
   P.counters = (unsigned long long *)io->d_counters;
   P.isa = c->d_isa[col]; P.spop = c->d_spop;
@@ -822,8 +850,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
   P.shmem_limited_broadcast = cfg.shmem_limited_broadcast; P.gmem_skip_L1D = cfg.gmem_skip_L1D;
 
   // what must start at zero: the table entries this call uses, the status block, the counters
-  CK(cudaMemsetAsync(P.state1, 0, (size_t)(n_chunks + 1) * sizeof(ti::State1), s));
-  CK(cudaMemsetAsync(P.state2, 0, (size_t)(n_chunks + 1) * sizeof(ti::State2), s));
+  CK(cudaMemsetAsync(scratch, 0, ti::chain_bytes(n_chunks), s));
   CK(cudaMemsetAsync(io->d_status, 0, sizeof(ti::Globals), s));
   CK(cudaMemsetAsync(&((ti::Globals *)io->d_status)->first_error_off, 0xff, 4, s));
   CK(cudaMemsetAsync(io->d_counters, 0, sizeof(ti_counters), s));

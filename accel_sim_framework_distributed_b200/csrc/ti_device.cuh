@@ -8,7 +8,7 @@
 //   txn_off   : u32[n_mem+1]          CSR offsets
 //   txn       : ti_txn_rec[n_txn]     32 B each
 //   tb / warp : per "thread block =" / "warp =" header
-//   state     : ChunkState[n_chunks]  decoupled look-back descriptors (scratch)
+//   chains    : u64[4][n_chunks+1]    decoupled look-back words (scratch)
 //
 // The shard is cut into fixed CHUNK-byte pieces; a chunk owns every line that
 // starts inside it.  A persistent grid takes chunks in file order from an atomic
@@ -94,17 +94,22 @@ TI_HD uint32_t isa_hash(uint64_t lo, uint32_t hi) {
   return (uint32_t)(x >> 17) & (kIsaSlots - 1);
 }
 
-// -------------------------------------------------------- look-back descriptors
-// One per chunk and per scan, zeroed before launch.  Every 64-bit word carries its own
-// "valid" bit next to the value, so a reader needs no fence: it either sees a complete
-// word or keeps polling (single-copy atomic 8-byte loads/stores).
-//   State1.agg : bit 63 valid | n_warp << 42 | n_tb << 28 | n_mem << 14 | n_inst   (this chunk)
-//   State1.inc0: bit 63 valid | mem << 31 | inst          (inclusive prefix, 31 bits each)
-//   State1.inc1: bit 63 valid | warp << 31 | tb
-//   State2.w   : bit 63 inclusive valid | bit 62 aggregate valid | transaction count
-struct State1 { unsigned long long agg, inc0, inc1, pad; };
-struct State2 { unsigned long long w; };
+// -------------------------------------------------------- look-back chains
+// Four chained scans run over the chunks, each a u64 array indexed by chunk, zeroed before
+// launch.  A word carries its own state next to the value, so a reader needs no fence: it
+// either sees a complete word or keeps polling (single-copy atomic 8-byte loads/stores).
+//   bit 63: the payload is this chunk's INCLUSIVE prefix   bit 62: it is this chunk's aggregate
+//   payload: two 31-bit fields, f0 | f1 << 31
+//   chain 0: instructions | thread-block headers     (published after P1, resolved before the records leave)
+//   chain 1: warp headers                            (same)
+//   chain 2: memory instructions                     (published after P3)
+//   chain 3: transactions                            (published after P7)
+// Chains 2 and 3 normally resolve one iteration later, when the chunk's address rows and
+// transactions leave (ti_kernel_main.cuh: finish); a chunk with warp-path instructions needs
+// the row index earlier and resolves chain 2 in its own iteration as well.
+constexpr int kChains = 4;
 constexpr unsigned long long kValid = 1ull << 63, kAggValid = 1ull << 62;
+constexpr size_t chain_bytes(size_t n_chunks) { return (size_t)kChains * 8 * (n_chunks + 1); }
 
 struct Globals {        // zeroed before launch (first_error_off: all ones)
   uint32_t ticket;      // next chunk to hand out
@@ -112,7 +117,8 @@ struct Globals {        // zeroed before launch (first_error_off: all ones)
   uint32_t first_error_off;
   uint32_t overflow;    // bit0 inst, bit1 mem, bit2 txn, bit3 tb, bit4 warp capacity exceeded
   uint32_t rare[4];     // how often the rare paths ran: [0] staging overflow (recompute), [1] headers not parked (early
-                        // resolve), [2] previous chunk's records reached into the parking area, [3] descriptor list full
+                        // resolve), [2] chunks that resolved the row index in their own iteration (warp-path
+                        // instructions), [3] descriptor list full
 };
 
 struct DecodeParams {
@@ -132,8 +138,7 @@ struct DecodeParams {
   // indices and text offsets stored in the records of a streamed shard are file-global
   uint64_t off_inst, off_mem, off_txn, off_warp, off_text;
   // scratch
-  State1 *state1;
-  State2 *state2;
+  unsigned long long *chain[kChains];   // each [n_chunks + 1], see "look-back chains"
   Globals *g;
   unsigned long long *counters;   // ti_counters viewed as u64[]
   // tables + model parameters

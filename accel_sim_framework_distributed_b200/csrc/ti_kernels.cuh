@@ -2,23 +2,22 @@
 //
 // Per chunk, one CTA runs these phases entirely out of shared memory:
 //   P0  stage-in    TMA bulk copy of [chunk-16, chunk+CHUNK+slack) -> smem, prefetched one chunk ahead
-//   P1  line index  newline + delimiter bitmaps (SWAR) -> line-start lists, by class
-//   P2  tokenize    thread-per-line decode of instruction lines -> 32 B records (smem)
-//   P3  compact     ordinal of every memory instruction, base+stride / other lists
-//   P4  publish #1  (n_inst, n_mem, n_tb, n_warp) of the chunk for the chained scan
+//   P1  line index  newline + delimiter bitmaps (SWAR) -> line-start lists, by class; publish chains 0/1
+//   P2  tokenize    thread-per-line decode of instruction lines -> 32 B records (smem): fast pass + general parser
+//   P3  compact     ordinal of every memory instruction, base+stride / other lists; publish chain 2
+//   F'  previous    the PREVIOUS chunk's address rows and transactions leave (chains 2/3 resolve here)
 //   P5  structure   "thread block" / "warp"+"insts" / "#BEGIN_TB" / "#END_TB" lines, parked chunk-relative
-//   P7' previous    look-back #2 of the PREVIOUS chunk resolves, its transactions leave in file order
-//   P6a stride      thread-per-instruction closed-form coalescing of base+stride lines -> smem
-//   P4' resolve #1  decoupled look-back -> global offsets for inst / mem / tb / warp
-//   P6b memory      warp-per-instruction: list / delta addresses -> 256 B row, coalescer -> smem
-//   P7  publish #2  scan of transaction counts, publish; next ticket + prefetch
-//   P6c / P8        parked headers, base+stride rows, records smem -> HBM; counters
+//   P6a stride      thread-per-instruction: base+stride lines -> 16 B descriptor + transaction count
+//   P6b memory      warp-per-instruction: list / delta addresses -> 256 B row, coalescer -> smem staging
+//   P7  scan        transaction offsets inside the chunk; publish chain 3; resolve chains 0/1; next ticket + prefetch
+//   P6c / P8        parked headers, records smem -> HBM (one TMA bulk store); counters
 #ifndef TI_KERNELS_CUH
 #define TI_KERNELS_CUH
 
 #include "ti_device.cuh"
 #include "ti_mem.cuh"
 #include "ti_parse.cuh"
+#include "ti_fast.cuh"
 
 #ifdef TI_EMU
 #define TI_DYN_SMEM(p) unsigned char *p = emu::cur_smem()
@@ -35,25 +34,30 @@ static inline unsigned __vcmpeq4(unsigned a, unsigned b) {
 namespace ti {
 
 // ------------------------------------------------------------ shared-memory plan
-struct LbWarp { uint32_t L; uint32_t s[4]; unsigned long long i0, i1; };  // see cta_lookback1
+struct LbWarp { uint32_t L[2]; uint32_t s[4]; unsigned long long inc[2]; };  // see cta_resolve
 struct Misc {
-  uint64_t base_inst, base_mem, base_tb, base_warp, base_txn;
   uint64_t warp_tot[kWarps];
-  uint32_t chunk, n_inst, n_sl, n_mem, n_tb, n_warp, n_txn;
-  uint32_t next_mem, stage_used, err, first_err, n_extra, chunk_next;
+  uint32_t n_tb, n_warp;
+  uint32_t next_mem, stage_used, err, first_err, n_extra, chunk_next, n_p2slow;
   uint64_t mbar[2];  // one mbarrier per text buffer (completion of the bulk copy)
   LbWarp lb[kWarps];  // per-warp partial results of the CTA-wide look-back
 };
 constexpr int align16(int x) { return (x + 15) & ~15; }
-constexpr int oText = 0;                                     // two text buffers: the chunk being decoded + the prefetched next one
+// The "pool" is shared by three tenants whose sizes vary from chunk to chunk: base+stride descriptors
+// (16 B each, from the bottom), transactions staged by the warp path (32 B slots, behind the
+// descriptors) and parked thread-block / warp headers (32 B slots, at the top).
+constexpr int kNoteCap = 256;                                // base+stride descriptors per chunk (more: warp path)
+constexpr int kParkMax = 128;                                // pool slots (32 B) lent to parked headers
+constexpr int oText = 0;                                     // text buffer(s): the chunk being decoded (+ the prefetched next one)
 constexpr int oRecs = oText + TI_TEXT_BUFS * kTextBytes;
-constexpr int oStage = oRecs + kRecCap * 32;
-constexpr int oInstOff = oStage + kTxnStage * 32;            // u16[kRecCap]  smem offset of each instruction line
+constexpr int oPool = oRecs + kRecCap * 32;
+constexpr int oInstOff = oPool + kTxnStage * 32;             // u16[kRecCap]  smem offset of each instruction line
 constexpr int oSlOff = oInstOff + align16(kRecCap * 2);      // u16[kSlCap]   smem offset of each structural line
-constexpr int oMemList = oSlOff + align16(kSlCap * 2);       // u16[kRecCap]  record index of each memory instruction
-constexpr int oFastList = oMemList + align16(kRecCap * 2);   // u16[kRecCap]  memory ordinals taking the thread-per-instruction path
+constexpr int oMemList = oSlOff + align16(kSlCap * 2);       // u16[2][kRecCap] record index of each memory instruction (by iteration parity:
+                                                             //               the previous chunk's list is read when its rows leave)
+constexpr int oFastList = oMemList + 2 * align16(kRecCap * 2);  // u16[kRecCap]  memory ordinals taking the thread-per-instruction path
 constexpr int oSlowList = oFastList + align16(kRecCap * 2);  // u16[kRecCap]  memory ordinals taking the warp-per-instruction path
-constexpr int oTxnSlot = oSlowList + align16(kRecCap * 2);   // u16[kRecCap]  staging slot (0xFFFF = recompute later)
+constexpr int oTxnSlot = oSlowList + align16(kRecCap * 2);   // u16[kRecCap]  0x8000 | descriptor index, or staging slot, or 0xFFFF = recompute later
 constexpr int oTxnLoc = oTxnSlot + align16(kRecCap * 2);     // u16[kRecCap]  exclusive txn offset inside the chunk
 constexpr int oTxnCnt = oTxnLoc + align16(kRecCap * 2);      // u8 [kRecCap]
 constexpr int oKind = oTxnCnt + align16(kRecCap);            // u8 [kRecCap]  bit0 = has addresses
@@ -62,18 +66,19 @@ constexpr int kWarpScratch = 32 * 6 * 4;                     // per warp: token 
 constexpr int oTok = oCnt + align16(kSmCnt * 4);
 constexpr int oNlMap = oTok + kWarps * kWarpScratch;      // u16[kTextBytes/16] newline bitmap of the staged text
 constexpr int oDlMap = oNlMap + align16(kTextBytes / 16 * 2 + 4);  // u16[kTextBytes/16] delimiter bitmap (' ', 0x09..0x0d)
-constexpr int oMisc = oDlMap + align16(kTextBytes / 16 * 2 + 4);
+constexpr int oMemo = oDlMap + align16(kTextBytes / 16 * 2 + 4);   // MemoEnt[kMemoSlots]: opcode string -> facts, kept for the CTA's life
+constexpr int oMisc = oMemo + kMemoSlots * (int)sizeof(MemoEnt);
 constexpr int kSmemBytes = oMisc + align16((int)sizeof(Misc));
 static_assert(kTextBytes % 16 == 0 && kChunk % 16 == 0 && kThreads % 32 == 0, "chunk geometry");
 static_assert(kTextBytes < 65536, "smem offsets are 16 bit");
-// Chunk-relative results parked until look-back #1 resolves (see P4 in ti_kernel_main.cuh):
-// thread-block / warp headers in the last slots of the staging area, base+stride descriptors
-// over the line-offset lists.
-constexpr int kParkMax = 128;                                // staging slots (32 B) lent to parked headers
-struct StrideNote { uint64_t base; int32_t stride; uint32_t flags; };
-constexpr uint32_t kNoteSkip = 1, kNoteEmpty = 2;            // handled by the warp path / no lane carries an address
+static_assert(TI_MIN_BLOCKS * (kSmemBytes + 1024) <= 233472, "TI_MIN_BLOCKS CTAs no longer fit into an SM's 228 KB of shared memory");
+// 16 B descriptor of a base+stride instruction: enough to write its address row and its transactions later
+//   meta: [4:0] first lane  [10:5] run length (0 = no lane carries an address)  [13:11] log2(data size)
+//         [15:14] segment (0: 32 B, 1: 64 B, 2: 128 B)  [16] write  [17] dense progression  [27:18] memory ordinal in the chunk
+struct StrideNote { uint64_t base; int32_t stride; uint32_t meta; };
 constexpr int kSlSplitMax = 96;                              // structural lines one warp handles beside P6a (3 rounds)
-static_assert(kParkMax < kTxnStage && oInstOff % 16 == 0 && oSlOff % 16 == 0 && sizeof(StrideNote) == 16, "parking areas");
+static_assert(kParkMax + kNoteCap / 2 < kTxnStage && oPool % 16 == 0 && sizeof(StrideNote) == 16, "pool tenants");
+static_assert(kRecCap <= 1024, "memory ordinals are 10 bit in StrideNote::meta");
 constexpr int kVecPerWarp = ((kChunk / 16 + kWarps - 1) / kWarps + 31) & ~31;  // 16 B vectors of the chunk per warp
 constexpr int kVecIters = kVecPerWarp / 32;
 
@@ -128,109 +133,81 @@ TI_D uint64_t warp_sum_u64(uint64_t v) {
   return v;
 }
 
-// Chained scan with decoupled look-back (single pass): publishes this chunk's
-// aggregate, sums the aggregates of the predecessors that have not finished yet plus
-// the nearest published inclusive prefix, then publishes its own inclusive prefix.
-// Chunks are handed out in order by the ticket, so every predecessor is already
-// running.  Executed by one full warp; lane k inspects chunk c-1-k.
+// ---- chained scans with decoupled look-back (single pass over the text).  A chunk publishes its
+// aggregate as early as it knows it and resolves -- sums the aggregates of the predecessors that have
+// not resolved yet plus the nearest published inclusive prefix -- as late as it can: a chunk resolves
+// only once EVERY chunk before it has published, i.e. at the running maximum of ~450 in-flight
+// predecessors' publish times, so everything that does not need the prefix sits between the two.
+// Chunks are handed out in order by the ticket, so every predecessor is already running.
 TI_D unsigned long long ld_vol64(const unsigned long long *p) { return *reinterpret_cast<const volatile unsigned long long *>(p); }
 TI_D void st_vol64(unsigned long long *p, unsigned long long v) { *reinterpret_cast<volatile unsigned long long *>(p) = v; }
+TI_HD unsigned long long chain_pack(uint32_t f0, uint32_t f1) { return (unsigned long long)f1 << 31 | f0; }
 
-// ---- CTA-wide look-back: thread t inspects chunk c-1-t, so one round covers kThreads
-// predecessors.  The persistent CTAs run phase-locked (equal work per chunk), so a chunk's
-// predecessors publish their aggregates at about the same moment as the chunk itself and
-// their inclusive prefixes only after their own look-back: the nearest inclusive prefix is
-// typically ~100 chunks back.  A single warp needed several dependent 32-wide rounds of L2
-// round trips for that (measured: 20% of the kernel); the whole CTA needs one.
-
-// Publish and resolve are separate calls: a chunk resolves only once EVERY chunk before it has
-// published, i.e. at the running maximum of ~300 in-flight predecessors' publish times, so
-// whatever work does not need the prefix is placed between the two calls to absorb that jitter.
-TI_D void cta_publish1(State1 *st, uint32_t c, const uint32_t (&agg)[4]) {
-  if (threadIdx.x == 0)
-    st_vol64(&st[c].agg, kValid | (unsigned long long)agg[3] << 42 | (unsigned long long)agg[2] << 28 |
-                             (unsigned long long)agg[1] << 14 | agg[0]);
+TI_D void chain_publish(unsigned long long *ch, uint32_t c, unsigned long long payload) {   // one thread
+  st_vol64(&ch[c], kAggValid | payload);
 }
 
-TI_D void cta_resolve1(State1 *st, uint32_t c, const uint32_t (&agg)[4], uint64_t (&excl)[4], LbWarp *lb) {
-  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
+// CTA-wide resolve of two chains at once (Y may be null): thread t inspects chunk c-1-t, so one round
+// covers kThreads predecessors (the persistent CTAs run phase-locked, so the nearest inclusive prefix is
+// typically ~100 chunks back: a single warp needed several dependent rounds of L2 round trips).
+// excl[0..1] = fields of X, excl[2..3] = fields of Y.  Publishes the inclusive prefixes.
+// The first round's loads can be issued ahead of time (cta_lookahead, a phase earlier) so that their L2
+// round trip is over when the resolve starts; words that were not ready then are simply polled again.
+struct LbPre { unsigned long long x, y; };
+TI_D LbPre cta_lookahead(const unsigned long long *X, const unsigned long long *Y, uint32_t c) {
+  LbPre p = {kValid, kValid};
+  const int64_t j = (int64_t)c - 1 - (int64_t)threadIdx.x;
+  if (j >= 0) { p.x = ld_vol64(&X[j]); if (Y) p.y = ld_vol64(&Y[j]); }
+  return p;
+}
+TI_D void cta_resolve(unsigned long long *X, unsigned long long *Y, uint32_t c, unsigned long long aggX, unsigned long long aggY,
+                      uint64_t (&excl)[4], LbWarp *lb, const LbPre *pre = nullptr) {
+  const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   excl[0] = excl[1] = excl[2] = excl[3] = 0;
 #ifdef TI_EXP_NOWAIT  // tuning experiment only (wrong output): what the kernel costs with no look-back at all
-  excl[0] = (uint64_t)c * 300; excl[1] = (uint64_t)c * 120; excl[2] = c; excl[3] = (uint64_t)c * 12;
   return;
 #endif
+  bool found_x = false, found_y = Y == nullptr;
   for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= kThreads) {
     const int64_t j = idx - (int64_t)threadIdx.x;
-    unsigned long long A = kValid, I0 = kValid, I1 = kValid;
+    unsigned long long x = kValid, y = kValid;             // before the first chunk: inclusive prefix 0
+    bool loaded = false;
+    if (pre && idx == (int64_t)c - 1) { x = pre->x; y = pre->y; loaded = true; }
     for (;;) {
-      if (j >= 0) { I0 = ld_vol64(&st[j].inc0); I1 = ld_vol64(&st[j].inc1); A = ld_vol64(&st[j].agg); }
-      if (__syncthreads_and((int)((((I0 & I1) | A) >> 63) & 1))) break;
+      if (j >= 0 && !loaded) { x = ld_vol64(&X[j]); if (Y) y = ld_vol64(&Y[j]); }
+      if (__syncthreads_and((int)((x >> 62) != 0 && (y >> 62) != 0))) break;
+      loaded = false;
       __nanosleep(64);
     }
-    const bool hasinc = (I0 & I1) >> 63;
-    const uint32_t have = __ballot_sync(kFull, hasinc);
-    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
-    const bool useagg = lane < L;
-    const uint32_t s0 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A & 0x3fff) : 0u);
-    const uint32_t s1 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 14 & 0x3fff) : 0u);
-    const uint32_t s2 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 28 & 0x3fff) : 0u);
-    const uint32_t s3 = __reduce_add_sync(kFull, useagg ? (uint32_t)(A >> 42 & 0x3fff) : 0u);
-    const unsigned long long i0 = __shfl_sync(kFull, I0, L & 31), i1 = __shfl_sync(kFull, I1, L & 31);
-    if (lane == 0) { lb[w].L = L; lb[w].s[0] = s0; lb[w].s[1] = s1; lb[w].s[2] = s2; lb[w].s[3] = s3; lb[w].i0 = i0; lb[w].i1 = i1; }
+    const uint32_t have_x = __ballot_sync(0xffffffffu, (x >> 63) != 0), have_y = __ballot_sync(0xffffffffu, (y >> 63) != 0);
+    const unsigned Lx = have_x ? (unsigned)(__ffs(have_x) - 1) : 32u, Ly = have_y ? (unsigned)(__ffs(have_y) - 1) : 32u;
+    const uint32_t s0 = __reduce_add_sync(0xffffffffu, lane < Lx ? (uint32_t)x & 0x7fffffffu : 0u);
+    const uint32_t s1 = __reduce_add_sync(0xffffffffu, lane < Lx ? (uint32_t)(x >> 31) & 0x7fffffffu : 0u);
+    uint32_t s2 = 0, s3 = 0;
+    if (Y) {
+      s2 = __reduce_add_sync(0xffffffffu, lane < Ly ? (uint32_t)y & 0x7fffffffu : 0u);
+      s3 = __reduce_add_sync(0xffffffffu, lane < Ly ? (uint32_t)(y >> 31) & 0x7fffffffu : 0u);
+    }
+    const unsigned long long ix = __shfl_sync(0xffffffffu, x, Lx & 31), iy = __shfl_sync(0xffffffffu, y, Ly & 31);
+    if (lane == 0) { lb[w].L[0] = Lx; lb[w].L[1] = Ly; lb[w].s[0] = s0; lb[w].s[1] = s1; lb[w].s[2] = s2; lb[w].s[3] = s3; lb[w].inc[0] = ix; lb[w].inc[1] = iy; }
     __syncthreads();
-    bool found = false;
-    for (unsigned k = 0; k < (unsigned)kWarps && !found; ++k) {   // warp k looked at nearer chunks than warp k+1
-      excl[0] += lb[k].s[0]; excl[1] += lb[k].s[1]; excl[2] += lb[k].s[2]; excl[3] += lb[k].s[3];
-      if (lb[k].L < 32) {
-        const unsigned long long a0 = lb[k].i0, a1 = lb[k].i1;
-        excl[0] += a0 & 0x7fffffffull; excl[1] += a0 >> 31 & 0x7fffffffull;
-        excl[2] += a1 & 0x7fffffffull; excl[3] += a1 >> 31 & 0x7fffffffull;
-        found = true;
+    for (unsigned k = 0; k < (unsigned)kWarps; ++k) {       // warp k looked at nearer chunks than warp k+1
+      if (!found_x) {
+        excl[0] += lb[k].s[0]; excl[1] += lb[k].s[1];
+        if (lb[k].L[0] < 32) { excl[0] += lb[k].inc[0] & 0x7fffffffull; excl[1] += lb[k].inc[0] >> 31 & 0x7fffffffull; found_x = true; }
+      }
+      if (!found_y) {
+        excl[2] += lb[k].s[2]; excl[3] += lb[k].s[3];
+        if (lb[k].L[1] < 32) { excl[2] += lb[k].inc[1] & 0x7fffffffull; excl[3] += lb[k].inc[1] >> 31 & 0x7fffffffull; found_y = true; }
       }
     }
-    if (found) break;  // (the next use of lb is behind other barriers)
-    __syncthreads();   // lb is reused by the next round
+    if (found_x && found_y) break;  // (the next use of lb is behind other barriers)
+    __syncthreads();                // lb is reused by the next round
   }
   if (threadIdx.x == 0) {
-    st_vol64(&st[c].inc0, kValid | (excl[1] + agg[1]) << 31 | (excl[0] + agg[0]));
-    st_vol64(&st[c].inc1, kValid | (excl[3] + agg[3]) << 31 | (excl[2] + agg[2]));
+    st_vol64(&X[c], kValid | chain_pack((uint32_t)(excl[0] + (aggX & 0x7fffffffu)), (uint32_t)(excl[1] + (aggX >> 31 & 0x7fffffffu))));
+    if (Y) st_vol64(&Y[c], kValid | chain_pack((uint32_t)(excl[2] + (aggY & 0x7fffffffu)), (uint32_t)(excl[3] + (aggY >> 31 & 0x7fffffffu))));
   }
-}
-
-TI_D void cta_publish2(State2 *st, uint32_t c, uint32_t agg) {
-  if (threadIdx.x == 0 && c) st_vol64(&st[c].w, kAggValid | agg);
-}
-
-TI_D uint64_t cta_resolve2(State2 *st, uint32_t c, uint32_t agg, LbWarp *lb) {
-  const unsigned lane = lane_id(), w = threadIdx.x >> 5;
-  uint64_t excl = 0;
-#ifdef TI_EXP_NOWAIT
-  return (uint64_t)c * 470;
-#endif
-  for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= kThreads) {
-    const int64_t j = idx - (int64_t)threadIdx.x;
-    unsigned long long W = kValid;
-    for (;;) {
-      if (j >= 0) W = ld_vol64(&st[j].w);
-      if (__syncthreads_and((int)((W >> 62) != 0))) break;
-      __nanosleep(64);
-    }
-    const uint32_t have = __ballot_sync(kFull, (W >> 63) != 0);
-    const unsigned L = have ? (unsigned)(__ffs(have) - 1) : 32u;
-    const uint32_t s0 = __reduce_add_sync(kFull, lane < L ? (uint32_t)(W & 0xffffffffull) : 0u);
-    const unsigned long long i0 = __shfl_sync(kFull, W, L & 31);
-    if (lane == 0) { lb[w].L = L; lb[w].s[0] = s0; lb[w].i0 = i0; }
-    __syncthreads();
-    bool found = false;
-    for (unsigned k = 0; k < (unsigned)kWarps && !found; ++k) {
-      excl += lb[k].s[0];
-      if (lb[k].L < 32) { excl += lb[k].i0 & 0x3fffffffffffffffull; found = true; }
-    }
-    if (found) break;
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) st_vol64(&st[c].w, kValid | (excl + agg));
-  return excl;
 }
 
 TI_D void note_error(Misc *ms, uint32_t flags, uint32_t off) {

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256) ti_local_kernel(const LocalParams L) {
       t.chunks = __reduce_or_sync(kFull, t.chunks);
 #pragma unroll
       for (int k = 0; k < 4; ++k) t.bytes[k] = __reduce_or_sync(kFull, t.bytes[k]);
-      if (L.txn && lane == 0 && base + n_txn < L.cap_txn) L.txn[base + n_txn] = reduce_and_send(t, seg, is_write ? 5u : 1u, is_write);   // LOCAL_ACC_W / LOCAL_ACC_R
+      if (L.txn && lane == 0 && base + n_txn < L.cap_txn) txn_store(L.txn + base + n_txn, reduce_and_send(t, seg, is_write ? 5u : 1u, is_write));   // LOCAL_ACC_W / LOCAL_ACC_R
       ++n_txn;
       last = blk;
       first = false;

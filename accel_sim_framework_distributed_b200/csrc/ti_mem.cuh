@@ -57,8 +57,11 @@ TI_D unsigned segment_size(const DecodeParams &P, unsigned data_size, unsigned c
   return 0;
 }
 
-// abstract_hardware_model.cc:694-748
-TI_D ti_txn_rec reduce_and_send(const Txn &t, unsigned seg, unsigned type, unsigned is_write) {
+// abstract_hardware_model.cc:694-748.  The finished mem_access_t as the two 16-byte halves of a
+// ti_txn_rec (addr | lane_mask | byte_mask[0] and byte_mask[1..3] | size, sector_mask, type, is_write),
+// built in registers: a struct with byte fields read back as vectors would live in local memory.
+struct TxnWords { uint4 a, b; };
+TI_D TxnWords reduce_and_send(const Txn &t, unsigned seg, unsigned type, unsigned is_write) {
   uint64_t addr = t.block;
   unsigned size = seg, q = t.chunks, h = 0;
   if (seg == 128) {
@@ -73,11 +76,14 @@ TI_D ti_txn_rec reduce_and_send(const Txn &t, unsigned seg, unsigned type, unsig
     if (lo && !hi) size = 32;
     else if (!lo && hi) { addr += 32; size = 32; }
   }
-  ti_txn_rec r;
-  r.addr = addr; r.lane_mask = t.lanes;
-  r.byte_mask[0] = t.bytes[0]; r.byte_mask[1] = t.bytes[1]; r.byte_mask[2] = t.bytes[2]; r.byte_mask[3] = t.bytes[3];
-  r.size = (uint8_t)size; r.sector_mask = (uint8_t)t.chunks; r.type = (uint8_t)type; r.is_write = (uint8_t)is_write;
+  TxnWords r;
+  r.a = make_uint4((uint32_t)addr, (uint32_t)(addr >> 32), t.lanes, t.bytes[0]);
+  r.b = make_uint4(t.bytes[1], t.bytes[2], t.bytes[3], size | (t.chunks & 0xff) << 8 | type << 16 | is_write << 24);
   return r;
+}
+TI_D void txn_store(ti_txn_rec *dst, const TxnWords &w) {
+  uint4 *d = reinterpret_cast<uint4 *>(dst);
+  d[0] = w.a; d[1] = w.b;
 }
 
 // ---- address decompression.  `q` = smem offset of the first token after the mode field, `le` =
@@ -176,8 +182,20 @@ struct StrideDesc {
   unsigned first, n;  // lanes [first, first + n) carry base + i * stride; every other lane reads 0
 };
 
-// Parses "0x<base> <stride>" at smem offset q.  Returns false when the progression wraps
-// around 2^64 (then it is not monotone and the warp path handles the instruction).
+// lanes of the first contiguous run of active lanes; false when the progression wraps around 2^64
+// (then it is not monotone and the warp path handles the instruction)
+TI_D bool stride_finish(uint32_t mask, unsigned ds, StrideDesc &d) {
+  if (!mask) return true;
+  d.first = __ffs(mask) - 1;
+  const uint32_t inv = ~(mask >> d.first);
+  d.n = inv ? __ffs(inv) - 1 : 32;
+  const uint64_t span = (uint64_t)(d.stride < 0 ? -d.stride : d.stride) * (d.n - 1);
+  if (d.stride >= 0) return d.base + span + (ds - 1) >= d.base;  // no overflow past 2^64
+  return d.base >= span && d.base + (ds - 1) >= d.base;
+}
+
+// Parses "0x<base> <stride>" at smem offset q (character loops: every shape the reference's stream
+// extraction accepts).  Returns stride_finish's verdict.
 TI_D bool stride_parse(const uint8_t *text, unsigned q, uint32_t mask, unsigned ds, StrideDesc &d, uint32_t &flags) {
   Reader rd = {text, (int)q};
   d.base = 0; d.stride = 0; d.first = 0; d.n = 0;
@@ -187,13 +205,7 @@ TI_D bool stride_parse(const uint8_t *text, unsigned q, uint32_t mask, unsigned 
     rd.skip_ws();
     if (rd.peek() != '\n' && !rd.sdec(0x7fffffffull, d.stride)) { flags |= TI_EF_BAD_NUMBER; return true; }
   }
-  if (!mask) return true;
-  d.first = __ffs(mask) - 1;
-  const uint32_t inv = ~(mask >> d.first);
-  d.n = inv ? __ffs(inv) - 1 : 32;
-  const uint64_t span = (uint64_t)(d.stride < 0 ? -d.stride : d.stride) * (d.n - 1);
-  if (d.stride >= 0) return d.base + span + (ds - 1) >= d.base;  // no overflow past 2^64
-  return d.base >= span && d.base + (ds - 1) >= d.base;
+  return stride_finish(mask, ds, d);
 }
 
 TI_D uint64_t stride_addr(const StrideDesc &d, unsigned lane) {
@@ -228,7 +240,7 @@ TI_D unsigned dense_count(const StrideDesc &d, unsigned ds, unsigned seg) {
   const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)d.n * ds;
   return (unsigned)((((end - 1) & segmask) - (d.base & segmask)) >> (__ffs(seg) - 1)) + 1;   // seg is 32, 64 or 128: no 64-bit division
 }
-TI_D unsigned dense_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out) {
+TI_D unsigned dense_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out, unsigned room = ~0u) {
   const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)d.n * ds;
   const unsigned sh = ds == 1 ? 0 : ds == 2 ? 1 : ds == 4 ? 2 : ds == 8 ? 3 : 4;
   unsigned n = 0;
@@ -247,12 +259,31 @@ TI_D unsigned dense_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigne
       x.bytes[w] = hit ? ((b - a == 32 ? 0xffffffffu : ((1u << (b - a)) - 1)) << (a - 32 * w)) : 0u;
       x.chunks |= hit ? 1u << w : 0u;
     }
-    const ti_txn_rec r = reduce_and_send(x, seg, type, is_write);
-    const uint4 *src = reinterpret_cast<const uint4 *>(&r);
-    uint4 *dst = reinterpret_cast<uint4 *>(out + n);
-    dst[0] = src[0]; dst[1] = src[1];
+    if (n < room) txn_store(out + n, reduce_and_send(x, seg, type, is_write));
   }
   return n;
+}
+
+// the k-th transaction of a dense progression, in closed form (one lane of a quad emits one transaction)
+TI_D TxnWords dense_txn(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, unsigned k) {
+  const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)d.n * ds;
+  const unsigned sh = __ffs(ds) - 1;
+  const uint64_t S = (d.base & segmask) + (uint64_t)k * seg;
+  const uint64_t lo = S > d.base ? S : d.base, hi = S + seg < end ? S + seg : end;
+  const unsigned i0 = (unsigned)((lo - d.base) >> sh), i1 = (unsigned)((hi - d.base) >> sh);  // lanes [i0, i1) of the run
+  const unsigned p0 = (unsigned)(lo & 127), p1 = p0 + (unsigned)(hi - lo);                 // bytes [p0, p1) of the 128 B line
+  Txn x;
+  x.block = S;
+  x.lanes = (i1 - i0 == 32 ? 0xffffffffu : ((1u << (i1 - i0)) - 1)) << (d.first + i0);
+  x.chunks = 0;
+#pragma unroll
+  for (unsigned w = 0; w < 4; ++w) {
+    const unsigned a = p0 > 32 * w ? p0 : 32 * w, b = p1 < 32 * w + 32 ? p1 : 32 * w + 32;
+    const bool hit = b > a;
+    x.bytes[w] = hit ? ((b - a == 32 ? 0xffffffffu : ((1u << (b - a)) - 1)) << (a - 32 * w)) : 0u;
+    x.chunks |= hit ? 1u << w : 0u;
+  }
+  return reduce_and_send(x, seg, type, is_write);
 }
 
 struct OpenTxn { uint32_t lanes, b0, b1, b2, b3, chunks; };
@@ -268,20 +299,17 @@ TI_D void open_touch(OpenTxn &t, uint64_t a, unsigned ds, unsigned lane) {
   t.chunks |= 1u << k;
   t.lanes |= 1u << lane;
 }
-TI_D void open_flush(const OpenTxn &t, uint64_t block, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out, unsigned &n) {
+TI_D void open_flush(const OpenTxn &t, uint64_t block, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out, unsigned &n, unsigned room) {
   if (!t.lanes) return;
   Txn x;
   x.block = block; x.lanes = t.lanes; x.bytes[0] = t.b0; x.bytes[1] = t.b1; x.bytes[2] = t.b2; x.bytes[3] = t.b3; x.chunks = t.chunks;
-  const ti_txn_rec r = reduce_and_send(x, seg, type, is_write);
-  const uint4 *src = reinterpret_cast<const uint4 *>(&r);
-  uint4 *dst = reinterpret_cast<uint4 *>(out + n);
-  dst[0] = src[0]; dst[1] = src[1];
+  if (n < room) txn_store(out + n, reduce_and_send(x, seg, type, is_write));
   ++n;
 }
 
 // writes the transactions in ascending block order (the std::map order of
 // abstract_hardware_model.cc:576-584); returns how many
-TI_D unsigned stride_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out) {
+TI_D unsigned stride_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsigned type, unsigned is_write, ti_txn_rec *out, unsigned room = ~0u) {
   const uint64_t segmask = ~(uint64_t)(seg - 1);
   OpenTxn c0, c1;             // blocks b and b + seg
   open_clear(c0); open_clear(c1);
@@ -293,17 +321,17 @@ TI_D unsigned stride_emit(const StrideDesc &d, unsigned ds, unsigned seg, unsign
     if (a == 0) continue;
     const uint64_t A = a & segmask, last = a + ds - 1;
     if (A != b) {               // every later touch is >= A: close what lies below it
-      open_flush(c0, b, seg, type, is_write, out, n);
+      open_flush(c0, b, seg, type, is_write, out, n, room);
       if (A == b + seg) { c0 = c1; }
-      else { open_flush(c1, b + seg, seg, type, is_write, out, n); open_clear(c0); }
+      else { open_flush(c1, b + seg, seg, type, is_write, out, n, room); open_clear(c0); }
       open_clear(c1);
       b = A;
     }
     open_touch(c0, a, ds, d.first + i);
     if ((last & segmask) != A) open_touch(c1, last, ds, d.first + i);   // the straddle rule, :559-571
   }
-  open_flush(c0, b, seg, type, is_write, out, n);
-  open_flush(c1, b + seg, seg, type, is_write, out, n);
+  open_flush(c0, b, seg, type, is_write, out, n, room);
+  open_flush(c1, b + seg, seg, type, is_write, out, n, room);
   return n;
 }
 

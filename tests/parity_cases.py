@@ -167,10 +167,11 @@ def run_streamed(tp, tmp_path, shard_bytes, **gen):
     tp.kernel_finalizer(k)
 
 
-def run_rare_paths(tp, tmp_path, n_units=20):
+def run_rare_paths(tp, tmp_path):
     """The kernel's rare per-chunk paths really run (ti_kernel_path_stats) and give oracle-identical
-    results: staging overflow + recompute, headers that cannot be parked (early look-back resolve),
-    and a previous chunk whose staged records reach into the next chunk's parking area."""
+    results: staging overflow + recompute, headers that cannot be parked (early resolve of the record
+    prefixes), chunks with warp-path instructions (early resolve of the row index) and a full
+    base+stride descriptor list."""
     tmp = str(tmp_path)
 
     def decode(img, name):
@@ -184,35 +185,14 @@ def run_rare_paths(tp, tmp_path, n_units=20):
         tp.kernel_finalizer(k)
         return stats
 
-    # [0] more transactions in a chunk than the staging area holds
-    lines = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (16 * i, 0x7F0000000000 + 4096 * i) for i in range(150)]
-    assert decode(edge_cases.image([(b, 0, 0, [lines, lines]) for b in range(2)]), "overflow")[0] > 0
+    # [0] the warp path stages more transactions in a chunk than the pool holds (base+delta lines, 32 sectors each),
+    # next to base+stride lines whose descriptors share the pool; [2] such chunks resolve the row index early
+    lines = ["%04x ffffffff 0 STG.E.64.SYS 2 R4 R6 8 2 0x%x %s 0" % (16 * i, 0x7F1000000000 + 8192 * i, " ".join(["260"] * 31)) for i in range(60)]
+    lines += ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (0x2000 + 16 * i, 0x7F0000000000 + 4096 * i) for i in range(60)]
+    st = decode(edge_cases.image([(b, 0, 0, [lines, lines]) for b in range(2)]), "overflow")
+    assert st[0] > 0 and st[2] > 0, list(st)
     # [1] more thread-block / warp headers in a chunk than the parking area holds
     assert decode(edge_cases.VALID["edge_many_headers"][0], "headers")[1] > 0
-    # [3] more base+stride instructions in a chunk than descriptors fit beside the structural-line list
-    lines = ["%04x 00000001 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 4 0" % (16 * i, 0x7F3000000000 + 256 * i) for i in range(700)]
+    # [3] more base+stride instructions in a chunk than descriptors fit
+    lines = ["%x 1 0 LDG 0 4 1 0x%x 4 0" % (16 * i, 0x7F3000000000 + 256 * i) for i in range(1500)]   # ~30 bytes: > 256 per chunk
     assert decode(edge_cases.image([(0, 0, 0, [lines, []])]), "notes_full")[3] > 0
-    # [2] the SAME CTA decodes a chunk that fills the staging area almost to the brim and then a chunk with many
-    # headers to park.  Units of exactly one chunk (12 KiB, padded with blank lines), four brim-full ones for
-    # every header-rich one, more units than resident CTAs so that every CTA sees several.
-    chunk = 12288
-    mem = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 128 0" % (16 * i, 0x7F0000000000 + 4096 * i) for i in range(18)]
-    mem += ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 4 0" % (0x1000 + 16 * i, 0x7F2000000000 + 128 * i) for i in range(13)]   # 18*32 + 13*4 = 628
-    pad = ["%04x ffffffff 1 R1 FADD 2 R2 R3 0 0" % (0x4000 + 16 * i) for i in range(200)]
-    img0 = edge_cases.image([])
-    head = img0[:tp.parse_header(np.frombuffer(img0, dtype=np.uint8)[:8192].copy()).body_offset]
-
-    def unit(tbs):
-        text = edge_cases.image(tbs)[len(head):].rstrip(b"\n") + b"\n"
-        assert len(text) <= chunk
-        return text + b"\n" * (chunk - len(text))
-
-    body, b = [], 0
-    for u in range(n_units):
-        if u % 5 == 4:
-            body.append(unit([(b + j, 0, 0, [["0000 ffffffff 1 R1 FADD 2 R2 R3 0 0"], []]) for j in range(16)]))
-            b += 16
-        else:
-            body.append(unit([(b, 0, 0, [mem + pad, []])]))
-            b += 1
-    assert decode(head + b"".join(body), "clash")[2] > 0

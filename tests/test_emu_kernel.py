@@ -56,3 +56,32 @@ def test_emu_streamed(emu_parser, tmp_path):
 
 def test_emu_rare_paths(emu_parser, tmp_path):
     parity_cases.run_rare_paths(emu_parser, tmp_path)
+
+
+def test_emu_fast_pass_covers_tracer_lines(emu_parser, tmp_path):
+    """P2's fast pass (csrc/ti_fast.cuh) takes the tracer-shaped lines once the CTA's opcode memo is
+    warm: on a many-chunk corpus most lines must have gone through it (ti_counters.reserved[4]) and the
+    result must still equal the oracle's (run_generated)."""
+    d = parity_cases.run_generated(emu_parser, tmp_path, profile=2, seed=77, n_tb=40, insts_per_warp=25)
+    assert int(d.counters["reserved"][4]) > 0.5 * len(d.inst), (int(d.counters["reserved"][4]), len(d.inst))
+    d = parity_cases.run_generated(emu_parser, tmp_path, profile=5, seed=78, n_tb=60, insts_per_warp=12, block_threads=128)
+    assert int(d.counters["reserved"][4]) > 0.3 * len(d.inst), (int(d.counters["reserved"][4]), len(d.inst))
+
+
+def test_emu_streamed_empty_tail_shards_and_error_offset(emu_parser, tmp_path):
+    """The host -> host pipeline with shards that come out empty (one thread block longer than a shard): the
+    CSR sentinel txn_off[n_mem] must survive, and the result must equal the one-piece decode."""
+    import os
+    import numpy as np
+    import harness
+    lines = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 4 0" % (16 * i, 0x7F0000000000 + 256 * i) for i in range(400)]
+    img = edge_cases.image([(0, 0, 0, [lines, lines])])
+    path = os.path.join(str(tmp_path), "one_big_tb.traceg")
+    open(path, "wb").write(img)
+    k = emu_parser.parse_kernel_info(path)
+    whole = k.run()
+    want_off = whole.txn_off.copy()
+    d = k.run_streamed(len(img) // 3)          # cuts come out as [0, len, len, len]
+    assert np.array_equal(d.txn_off, want_off)
+    assert int(d.txn_off[-1]) == len(d.txn)
+    emu_parser.kernel_finalizer(k)

@@ -77,6 +77,20 @@ def test_staging_overflow_and_capacity_retry(cuda_parser, tmp_path):
     cuda_parser.kernel_finalizer(k)
 
 
+def test_streamed_empty_tail_shards(cuda_parser, tmp_path):
+    """One thread block longer than a shard: ti_plan_shards returns empty tail shards; the pipelined path must
+    still return the one-piece result, CSR sentinel included."""
+    lines = ["%04x ffffffff 1 R2 LDG.E.SYS 1 R4 4 1 0x%x 4 0" % (16 * i, 0x7F0000000000 + 256 * i) for i in range(400)]
+    img = edge_cases.image([(0, 0, 0, [lines, lines])])
+    path = os.path.join(str(tmp_path), "one_big_tb.traceg")
+    open(path, "wb").write(img)
+    k = cuda_parser.parse_kernel_info(path)
+    want = k.run().txn_off.copy()
+    d = k.run_streamed(len(img) // 3)
+    assert np.array_equal(d.txn_off, want) and int(d.txn_off[-1]) == len(d.txn)
+    cuda_parser.kernel_finalizer(k)
+
+
 def test_full_size_properties(cuda_parser):
     """Size-independent properties at BASELINE.json's full config-2 size (1.05 GB of text, 100 000
     thread blocks -- far too large for the CPU oracle to check in seconds): determinism, CSR
@@ -150,4 +164,4 @@ def test_streamed_host_path(cuda_parser, tmp_path, shard_bytes):
 
 
 def test_rare_paths(cuda_parser, tmp_path):
-    parity_cases.run_rare_paths(cuda_parser, tmp_path, n_units=2000)   # more chunks than resident CTAs (444)
+    parity_cases.run_rare_paths(cuda_parser, tmp_path)   # more chunks than resident CTAs (444)
