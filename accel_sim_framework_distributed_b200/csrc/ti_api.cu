@@ -767,7 +767,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
 // The only memory the decode needs beyond its inputs and outputs is the set of
 // per-chunk look-back tables.  For this entry point they live in the file-scope device
 // array below instead of a cudaMalloc'ed buffer: (TI_NOALLOC_MAX_TEXT / chunk + 2)
-// entries of 32 bytes, about 0.7 MB, resident on every GPU that loads the library
+// entries of 32 bytes, about 0.5 MB, resident on every GPU that loads the library
 // for as long as the process lives.
 //
 // In host code the name `g_noalloc_scratch` is only a handle for the symbol, not an
@@ -782,7 +782,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
 namespace {
 constexpr size_t kNoallocChunks = (size_t)(TI_NOALLOC_MAX_TEXT / ti::kChunk) + 2;
 constexpr size_t kNoallocBytes = ti::chain_bytes(kNoallocChunks - 1);
-static_assert(ti::kChunk != 12288 || kNoallocBytes == TI_NOALLOC_SCRATCH_BYTES,  // (tuning builds use other chunk sizes)
+static_assert(ti::kChunk != 18432 || kNoallocBytes == TI_NOALLOC_SCRATCH_BYTES,  // (tuning builds use other chunk sizes)
               "TI_NOALLOC_SCRATCH_BYTES in traceingest.h must state the real size of the scratch array");
 constexpr int kMaxDevices = 64;
 void *g_noalloc_addr[kMaxDevices];  // device address of the array, per device ordinal (0 = not looked up yet)

@@ -42,13 +42,13 @@ namespace ti {
 
 // ------------------------------------------------------------------ tunables
 #ifndef TI_CHUNK
-#define TI_CHUNK 12288
+#define TI_CHUNK 18432   // = warps per CTA x 1536: a warp owns 1536 bytes of the chunk (about one line per lane)
 #endif
 #ifndef TI_THREADS
-#define TI_THREADS 256
+#define TI_THREADS 384
 #endif
 #ifndef TI_TXN_STAGE
-#define TI_TXN_STAGE 640
+#define TI_TXN_STAGE 672
 #endif
 #ifndef TI_TEXT_BUFS
 #define TI_TEXT_BUFS 1     // text buffers; the text is dead after P6b, so one buffer takes the prefetch of the next chunk too
@@ -57,7 +57,7 @@ namespace ti {
 #define TI_TMA_STORE 1     // P8: the chunk's record block leaves shared memory as one TMA bulk store
 #endif
 #ifndef TI_MIN_BLOCKS
-#define TI_MIN_BLOCKS 3   // resident CTAs per SM the register allocation is bounded for
+#define TI_MIN_BLOCKS 2   // resident CTAs per SM the register allocation is bounded for
 #endif
 constexpr int kChunk = TI_CHUNK;        // bytes of text owned by one chunk
 constexpr int kThreads = TI_THREADS;    // threads per CTA

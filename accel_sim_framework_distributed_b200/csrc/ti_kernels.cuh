@@ -1,16 +1,21 @@
 // The fused trace-ingest kernel (see ti_device.cuh for the data layout, DESIGN.md 3 for the plan).
 //
-// Per chunk, one CTA runs these phases entirely out of shared memory:
+// A chunk is cut into one byte range per warp; a warp owns the lines that START in its range and takes
+// them through tokenizing, base+stride parsing and transaction counting on its own, so that the CTA
+// meets at a barrier only a few times per chunk:
 //   P0  stage-in    TMA bulk copy of [chunk-16, chunk+CHUNK+slack) -> smem, prefetched one chunk ahead
-//   P1  line index  newline + delimiter bitmaps (SWAR) -> line-start lists, by class; publish chains 0/1
-//   P2  tokenize    thread-per-line decode of instruction lines -> 32 B records (smem): fast pass + general parser
-//   P3  compact     ordinal of every memory instruction, base+stride / other lists; publish chain 2
-//   F'  previous    the PREVIOUS chunk's address rows and transactions leave (chains 2/3 resolve here)
-//   P5  structure   "thread block" / "warp"+"insts" / "#BEGIN_TB" / "#END_TB" lines, parked chunk-relative
-//   P6a stride      thread-per-instruction: base+stride lines -> 16 B descriptor + transaction count
-//   P6b memory      warp-per-instruction: list / delta addresses -> 256 B row, coalescer -> smem staging
-//   P7  scan        transaction offsets inside the chunk; publish chain 3; resolve chains 0/1; next ticket + prefetch
-//   P6c / P8        parked headers, records smem -> HBM (one TMA bulk store); counters
+//   P1  classify    newline + delimiter bitmaps of the staged text (SWAR), all threads          | barrier
+//   W   per warp    line starts of the range -> per-warp line lists; a lane per instruction line:
+//                   fast tokenizer (general parser for what it declines) -> 32 B record in the warp's
+//                   record region; base+stride lines -> 16 B descriptor + transaction count; counters;
+//                   warp totals                                                                 | barrier
+//   S   prefixes    per-warp offsets inside the chunk from the eight totals; publish chains 0 / 1 / 2
+//   F'  previous    the PREVIOUS chunk's address rows and transactions leave (chains 2 / 3 resolve)
+//   H   headers     "thread block" / "warp"+"insts" / "#BEGIN_TB" / "#END_TB" lines, per warp, parked
+//   M   memory      (only chunks that have any) warp-per-instruction: list / delta addresses -> 256 B
+//                   row, coalescer -> smem staging; needs chain 2 now                            | barrier
+//   T   publish chain 3; next ticket + prefetch; resolve chains 0 / 1; parked headers out; every warp
+//       sends its record region with one TMA bulk store
 #ifndef TI_KERNELS_CUH
 #define TI_KERNELS_CUH
 
@@ -35,33 +40,38 @@ namespace ti {
 
 // ------------------------------------------------------------ shared-memory plan
 struct LbWarp { uint32_t L[2]; uint32_t s[4]; unsigned long long inc[2]; };  // see cta_resolve
+// what a warp found in its byte range / where its results start inside the chunk
+struct WarpTot { uint16_t n_inst, n_sl, n_tb, n_warp, n_mem, n_notes; uint32_t n_txn; };
+struct WarpPre { uint16_t inst0, mem0, n_mem, n_notes; uint32_t txn0; };   // kept for the iteration in which the chunk's rows leave
 struct Misc {
-  uint64_t warp_tot[kWarps];
-  uint32_t n_tb, n_warp;
-  uint32_t next_mem, stage_used, err, first_err, n_extra, chunk_next, n_p2slow;
+  WarpTot wt[kWarps];
+  WarpPre pw[2][kWarps];
+  uint32_t next_mem, stage_used, err, first_err, n_slowq, chunk_next, n_general;
   uint64_t mbar[2];  // one mbarrier per text buffer (completion of the bulk copy)
   LbWarp lb[kWarps];  // per-warp partial results of the CTA-wide look-back
 };
 constexpr int align16(int x) { return (x + 15) & ~15; }
-// The "pool" is shared by three tenants whose sizes vary from chunk to chunk: base+stride descriptors
-// (16 B each, from the bottom), transactions staged by the warp path (32 B slots, behind the
-// descriptors) and parked thread-block / warp headers (32 B slots, at the top).
-constexpr int kNoteCap = 256;                                // base+stride descriptors per chunk (more: warp path)
+constexpr int kRange = kChunk / kWarps;                      // bytes of the chunk a warp owns
+constexpr int kLaneBits = kRange / 32;                       // ... and a lane scans for line starts
+constexpr int kWarpInst = kRange / 24;                       // instruction lines a range can hold (no tracer line is shorter than 24 bytes)
+constexpr int kWarpSl = kRange / 8;                          // structural lines ("#END_TB\n")
+constexpr int kItems = kWarps * kWarpInst;                   // memory-instruction slots of a chunk: warp w owns [w * kWarpInst, ...)
+constexpr int kNotesPerWarp = 32;                            // base+stride descriptors per warp and chunk (more: warp path)
 constexpr int kParkMax = 128;                                // pool slots (32 B) lent to parked headers
+static_assert(kChunk % (kWarps * 32) == 0 && kLaneBits <= 64 && kLaneBits >= 16 && kRange % 16 == 0, "range geometry");
+static_assert(kWarpInst <= 255 && kItems <= 1024, "local line indices are 8 bit, item ids 10 bit");
 constexpr int oText = 0;                                     // text buffer(s): the chunk being decoded (+ the prefetched next one)
-constexpr int oRecs = oText + TI_TEXT_BUFS * kTextBytes;
-constexpr int oPool = oRecs + kRecCap * 32;
-constexpr int oInstOff = oPool + kTxnStage * 32;             // u16[kRecCap]  smem offset of each instruction line
-constexpr int oSlOff = oInstOff + align16(kRecCap * 2);      // u16[kSlCap]   smem offset of each structural line
-constexpr int oMemList = oSlOff + align16(kSlCap * 2);       // u16[2][kRecCap] record index of each memory instruction (by iteration parity:
-                                                             //               the previous chunk's list is read when its rows leave)
-constexpr int oFastList = oMemList + 2 * align16(kRecCap * 2);  // u16[kRecCap]  memory ordinals taking the thread-per-instruction path
-constexpr int oSlowList = oFastList + align16(kRecCap * 2);  // u16[kRecCap]  memory ordinals taking the warp-per-instruction path
-constexpr int oTxnSlot = oSlowList + align16(kRecCap * 2);   // u16[kRecCap]  0x8000 | descriptor index, or staging slot, or 0xFFFF = recompute later
-constexpr int oTxnLoc = oTxnSlot + align16(kRecCap * 2);     // u16[kRecCap]  exclusive txn offset inside the chunk
-constexpr int oTxnCnt = oTxnLoc + align16(kRecCap * 2);      // u8 [kRecCap]
-constexpr int oKind = oTxnCnt + align16(kRecCap);            // u8 [kRecCap]  bit0 = has addresses
-constexpr int oCnt = oKind + align16(kRecCap);               // u32[kSmCnt]   counter mirror
+constexpr int oRecs = oText + TI_TEXT_BUFS * kTextBytes;     // ti_inst_rec[kWarps][kWarpInst]
+constexpr int oPool = oRecs + kItems * 32;                   // 32 B slots: warp-path transactions from the bottom, parked headers at the top
+constexpr int oNotes = oPool + kTxnStage * 32;               // StrideNote[2][kWarps][kNotesPerWarp], by iteration parity
+constexpr int oWlInst = oNotes + 2 * kWarps * kNotesPerWarp * 16;   // u16[kWarps][kWarpInst] smem offset of each instruction line
+constexpr int oWlSl = oWlInst + align16(kItems * 2);         // u16[kWarps][kWarpSl]   smem offset of each structural line
+constexpr int oTxnSlot = oWlSl + align16(kWarps * kWarpSl * 2);  // u16[2][kItems] 0x8000 | descriptor index, or staging slot, or 0xFFFF = recompute later
+constexpr int oTxnLoc = oTxnSlot + 2 * align16(kItems * 2);  // u16[2][kItems] exclusive txn offset inside the warp's range
+constexpr int oTxnCnt = oTxnLoc + 2 * align16(kItems * 2);   // u8 [2][kItems]
+constexpr int oMIo = oTxnCnt + 2 * align16(kItems);          // u8 [2][kItems] index of the instruction among the warp's records
+constexpr int oSlowQ = oMIo + 2 * align16(kItems);           // u16[kItems]    items waiting for the warp path
+constexpr int oCnt = oSlowQ + align16(kItems * 2);           // u32[kSmCnt]    counter mirror
 constexpr int kWarpScratch = 32 * 6 * 4;                     // per warp: token offsets (decode), then B-group merge slots (coalesce)
 constexpr int oTok = oCnt + align16(kSmCnt * 4);
 constexpr int oNlMap = oTok + kWarps * kWarpScratch;      // u16[kTextBytes/16] newline bitmap of the staged text
@@ -74,13 +84,10 @@ static_assert(kTextBytes < 65536, "smem offsets are 16 bit");
 static_assert(TI_MIN_BLOCKS * (kSmemBytes + 1024) <= 233472, "TI_MIN_BLOCKS CTAs no longer fit into an SM's 228 KB of shared memory");
 // 16 B descriptor of a base+stride instruction: enough to write its address row and its transactions later
 //   meta: [4:0] first lane  [10:5] run length (0 = no lane carries an address)  [13:11] log2(data size)
-//         [15:14] segment (0: 32 B, 1: 64 B, 2: 128 B)  [16] write  [17] dense progression  [27:18] memory ordinal in the chunk
+//         [15:14] segment (0: 32 B, 1: 64 B, 2: 128 B)  [16] write  [17] dense progression  [27:18] item (memory-instruction slot)
+//         [28] void: the warp path took the instruction after all
 struct StrideNote { uint64_t base; int32_t stride; uint32_t meta; };
-constexpr int kSlSplitMax = 96;                              // structural lines one warp handles beside P6a (3 rounds)
-static_assert(kParkMax + kNoteCap / 2 < kTxnStage && oPool % 16 == 0 && sizeof(StrideNote) == 16, "pool tenants");
-static_assert(kRecCap <= 1024, "memory ordinals are 10 bit in StrideNote::meta");
-constexpr int kVecPerWarp = ((kChunk / 16 + kWarps - 1) / kWarps + 31) & ~31;  // 16 B vectors of the chunk per warp
-constexpr int kVecIters = kVecPerWarp / 32;
+static_assert(kParkMax < kTxnStage && oPool % 16 == 0 && oNotes % 16 == 0 && sizeof(StrideNote) == 16, "pool tenants");
 
 // ---- TMA 1-D bulk copy (cp.async.bulk, SASS UBLKCP) + mbarrier, used to prefetch the
 // next chunk's text while the current one is decoded.  Under the emulator the copy is a

@@ -29,9 +29,8 @@ tp.lib.ti_debug_phase_cycles(out)
 k.decode(); k.sync()
 ms = k.decode_ms()
 tp.lib.ti_debug_phase_cycles(out)
-names = ["top/ticket/edges", "P0 wait text", "P1 line index + publish 0/1", "P2 tokenize", "P3 mem ordinals + publish 2",
-         "F' previous chunk out (resolve 2/3)", "P5 CTA-wide / early resolve 0/1", "P6a stride path", "early resolve 2",
-         "P6b warp path", "P7 scan + publish 3", "resolve 0/1", "P6c + P8 headers, records, counters", "F own chunk (staging overflow)", "-"]
+names = ["top of loop", "P0 wait text", "P1 classify", "W line starts", "W tokenize + stride + counters", "S prefixes + F' previous chunk out",
+         "H structural lines", "M warp path", "T resolve chains 0/1", "headers + records out", "F own chunk (staging overflow)", "-", "-", "-", "-"]
 tot = sum(out[:15])
 print("decode %.3f ms; thread-0 cycles per phase (share of the CTA's time):" % ms)
 for n, v in zip(names, out):
