@@ -158,6 +158,77 @@ def test_full_size_properties(cuda_parser):
     cuda_parser.kernel_finalizer(k)
 
 
+def test_config2_full_size_vs_reference(cuda_parser, tmp_path):
+    """BASELINE.json config 2 at its full size (1.05 GB of text, 20 M instructions) against the reference-built
+    oracle, array by array: the body is cut into one whole-thread-block slice per host core, `ref_oracle dump`
+    runs on the slices in parallel, and every slice's records / address rows / CSR offsets / transactions /
+    thread-block and warp tables are compared bit for bit with the matching part of ONE one-piece GPU decode
+    (indices that the oracle counts from the start of its slice are shifted by what the earlier slices hold).
+    The integer counters of the slices must add up to the GPU's.  Pins what no smaller test reaches: offsets
+    beyond 2^24 instructions, the 31-bit prefix fields of the look-back words, look-back chains over more
+    chunks than resident CTAs."""
+    import subprocess
+    import time
+    import bench
+    t_start = time.time()
+    N_TB = 100000
+    img = harness.generate_bytes(profile=2, seed=2, n_tb=N_TB, insts_per_warp=25)
+    hdr = cuda_parser.parse_header(img[:4096])
+    body = img[hdr.body_offset:]
+    k = cuda_parser.open_buffer(body, hdr)
+    d = k.run()
+    kind = harness.oracle_kind()
+    exe = harness.REF_ORACLE if kind == "reference" else harness.PORT_ORACLE
+    n_slices = max(2, min(os.cpu_count() or 2, 32))
+    paths, total = bench.split_sample(img, hdr.body_offset, n_slices, (len(body) + n_slices - 1) // n_slices, str(tmp_path))
+    assert total == len(body)
+    acc = np.zeros(1, dtype=T.COUNTERS)
+    i0 = m0 = x0 = b0 = w0 = 0          # instructions, rows, transactions, thread blocks, warps before the slice
+    text0 = 0
+    wave = max(1, n_slices // 2)        # two waves: half of the dumps (about 2 GB) on disk at a time
+    for lo in range(0, len(paths), wave):
+        part = paths[lo:lo + wave]
+        procs = [subprocess.Popen([exe, "dump", p, p + ".tidump"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL) for p in part]
+        assert all(pr.wait() == 0 for pr in procs)
+        for p in part:
+            o = T.load_dump(p + ".tidump")
+            ni, nm, nx, nb, nw = len(o.inst), len(o.rows), len(o.txn), len(o.tb), len(o.warp)
+            g = d.inst[i0:i0 + ni]
+            assert len(g) == ni
+            for f in T.INST.names:
+                if f == "opc_off":
+                    continue                      # the oracles keep the opcode strings, not offsets
+                want = o.inst[f]
+                if f == "mem_idx":
+                    want = np.where(want != 0xFFFFFFFF, want + np.uint32(m0), want)
+                assert np.array_equal(g[f], want), (p, "inst." + f)
+            assert np.array_equal(d.rows[m0:m0 + nm], o.rows), (p, "rows")
+            assert np.array_equal(d.txn_off[m0:m0 + nm + 1].astype(np.int64) - x0, o.txn_off.astype(np.int64)), (p, "txn_off")
+            assert np.array_equal(d.txn[x0:x0 + nx], o.txn), (p, "txn")
+            gt, gw = d.tb[b0:b0 + nb], d.warp[w0:w0 + nw]
+            for f in ("x", "y", "z"):
+                assert np.array_equal(gt[f], o.tb[f]), (p, "tb." + f)
+            assert np.array_equal(gt["first_warp"], o.tb["first_warp"] + np.uint32(w0)) and np.array_equal(gt["first_inst"], o.tb["first_inst"] + np.uint32(i0)), (p, "tb")
+            assert np.array_equal(gw["warp_id"], o.warp["warp_id"]) and np.array_equal(gw["n_insts"], o.warp["n_insts"]), (p, "warp")
+            assert np.array_equal(gw["first_inst"], o.warp["first_inst"] + np.uint32(i0)), (p, "warp.first_inst")
+            # opcode tokens through the GPU's text offsets: the slice's first and last instruction and 200 random ones
+            for j in [0, ni - 1] + list(np.random.default_rng(lo).integers(0, ni, 200)):
+                r = g[int(j)]
+                assert bytes(body[int(r["opc_off"]):int(r["opc_off"]) + int(r["opcode_len"])]) == o.opcodes[int(j)], (p, "opcode", j)
+            c1 = np.zeros(1, dtype=T.COUNTERS)
+            c1[0] = o.counters
+            cuda_parser.lib.ti_counters_add(acc.ctypes.data, c1.ctypes.data)
+            i0 += ni; m0 += nm; x0 += nx; b0 += nb; w0 += nw
+            os.remove(p + ".tidump")
+            os.remove(p)
+    assert (i0, m0, x0, b0, w0) == (len(d.inst), len(d.rows), len(d.txn), len(d.tb), len(d.warp))
+    for f in T.COUNTERS.names:
+        if f not in ("reserved", "text_bytes", "n_begin_tb", "n_end_tb", "n_warp", "n_mem"):
+            assert np.array_equal(acc[0][f], d.counters[f]), f
+    cuda_parser.kernel_finalizer(k)
+    print("full-size differential test: %d slices, oracle=%s, %.1f s" % (len(paths), kind, time.time() - t_start))
+
+
 @pytest.mark.parametrize("shard_bytes", [1 << 20, 300000])
 def test_streamed_host_path(cuda_parser, tmp_path, shard_bytes):
     parity_cases.run_streamed(cuda_parser, tmp_path, shard_bytes, profile=5, seed=31, n_tb=800, insts_per_warp=10, block_threads=128)
