@@ -396,12 +396,19 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     TI_STAMP(4);   // W
 
     // ---------------------------------------------------------------- S offsets of the warps inside the chunk; chains 0 / 1 / 2
-    uint32_t n_inst = 0, n_sl = 0, n_tb = 0, n_warp = 0, n_mem = 0, n_txn_chunk = 0;
-    uint32_t inst0 = 0, tb0 = 0, warp0 = 0, mem0 = 0, txn0 = 0;
-    for (unsigned k = 0; k < (unsigned)kWarps; ++k) {
-      const WarpTot t = ms->wt[k];
-      if (k < wid) { inst0 += t.n_inst; tb0 += t.n_tb; warp0 += t.n_warp; mem0 += t.n_mem; txn0 += t.n_txn; }
-      n_inst += t.n_inst; n_sl += t.n_sl; n_tb += t.n_tb; n_warp += t.n_warp; n_mem += t.n_mem; n_txn_chunk += t.n_txn;
+    // (lane k takes warp k's totals; sums and the sums over the warps before this one by warp reductions)
+    uint32_t n_inst, n_sl, n_tb, n_warp, n_mem, n_txn_chunk, inst0, tb0, warp0, mem0, txn0;
+    {
+      const bool in = lane < (unsigned)kWarps, before = lane < wid;
+      WarpTot t = ms->wt[in ? lane : 0];
+      if (!in) { t.n_inst = t.n_sl = t.n_tb = t.n_warp = t.n_mem = 0; t.n_txn = 0; }
+      // two 16-bit counts per reduction: no field of a chunk exceeds 16 bits
+      const uint32_t a = t.n_inst | (uint32_t)t.n_tb << 16, b = t.n_warp | (uint32_t)t.n_mem << 16;
+      const uint32_t sa = __reduce_add_sync(kFull, a), sb = __reduce_add_sync(kFull, b), pa = __reduce_add_sync(kFull, before ? a : 0u), pb = __reduce_add_sync(kFull, before ? b : 0u);
+      n_inst = sa & 0xffff; n_tb = sa >> 16; n_warp = sb & 0xffff; n_mem = sb >> 16;
+      inst0 = pa & 0xffff; tb0 = pa >> 16; warp0 = pb & 0xffff; mem0 = pb >> 16;
+      n_sl = __reduce_add_sync(kFull, (uint32_t)t.n_sl);
+      n_txn_chunk = __reduce_add_sync(kFull, t.n_txn); txn0 = __reduce_add_sync(kFull, before ? t.n_txn : 0u);
     }
     const uint32_t n_warp_path = ms->n_slowq;               // CTA-uniform
     if (lane == 0) { WarpPre q; q.inst0 = (uint16_t)inst0; q.mem0 = (uint16_t)mem0; q.n_mem = (uint16_t)mem_seen; q.n_notes = (uint16_t)n_notes_w; q.txn0 = txn0; ms->pw[par][wid] = q; }
@@ -430,6 +437,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     if (!late) {
       cta_resolve(P.chain[0], P.chain[1], chunk, aggA0, aggA1, exA, ms->lb);
       if (tid == 0) atomicAdd(&P.g->rare[1], 1u);
+      __syncthreads();                                     // Misc::lb may be written again by the next resolve
     }
 
     // ---------------------------------------------------------------- H structural lines of the warp's range
@@ -571,8 +579,10 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       }
       if (lane == 0) ms->wt[wid].n_txn = seen;
       __syncthreads();
-      n_txn_chunk = 0; txn0 = 0;
-      for (unsigned k = 0; k < (unsigned)kWarps; ++k) { const uint32_t t = ms->wt[k].n_txn; if (k < wid) txn0 += t; n_txn_chunk += t; }
+      {
+        const uint32_t t = lane < (unsigned)kWarps ? ms->wt[lane].n_txn : 0u;
+        n_txn_chunk = __reduce_add_sync(kFull, t); txn0 = __reduce_add_sync(kFull, lane < wid ? t : 0u);
+      }
       if (lane == 0) ms->pw[par][wid].txn0 = txn0;
     }
     const uint32_t stage_used = ms->stage_used;        // final

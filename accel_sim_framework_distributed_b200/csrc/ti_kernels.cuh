@@ -79,7 +79,7 @@ constexpr int oDlMap = oNlMap + align16(kTextBytes / 16 * 2 + 4);  // u16[kTextB
 constexpr int oMemo = oDlMap + align16(kTextBytes / 16 * 2 + 4);   // MemoEnt[kMemoSlots]: opcode string -> facts, kept for the CTA's life
 constexpr int oMisc = oMemo + kMemoSlots * (int)sizeof(MemoEnt);
 constexpr int kSmemBytes = oMisc + align16((int)sizeof(Misc));
-static_assert(kTextBytes % 16 == 0 && kChunk % 16 == 0 && kThreads % 32 == 0, "chunk geometry");
+static_assert(kTextBytes % 16 == 0 && kChunk % 16 == 0 && kThreads % 32 == 0 && kWarps <= 32, "chunk geometry");
 static_assert(kTextBytes < 65536, "smem offsets are 16 bit");
 static_assert(TI_MIN_BLOCKS * (kSmemBytes + 1024) <= 233472, "TI_MIN_BLOCKS CTAs no longer fit into an SM's 228 KB of shared memory");
 // 16 B descriptor of a base+stride instruction: enough to write its address row and its transactions later
@@ -178,13 +178,15 @@ TI_D void cta_resolve(unsigned long long *X, unsigned long long *Y, uint32_t c, 
   for (int64_t idx = (int64_t)c - 1; idx >= 0; idx -= kThreads) {
     const int64_t j = idx - (int64_t)threadIdx.x;
     unsigned long long x = kValid, y = kValid;             // before the first chunk: inclusive prefix 0
-    bool loaded = false;
-    if (pre && idx == (int64_t)c - 1) { x = pre->x; y = pre->y; loaded = true; }
+    if (pre && idx == (int64_t)c - 1) { x = pre->x; y = pre->y; }
+    else if (j >= 0) { x = ld_vol64(&X[j]); if (Y) y = ld_vol64(&Y[j]); }
+    // every warp polls its own 32 predecessors: a warp whose words are all there goes on to the barrier
+    // below and costs no issue slots while another one still waits for a publish
     for (;;) {
-      if (j >= 0 && !loaded) { x = ld_vol64(&X[j]); if (Y) y = ld_vol64(&Y[j]); }
-      if (__syncthreads_and((int)((x >> 62) != 0 && (y >> 62) != 0))) break;
-      loaded = false;
-      __nanosleep(64);
+      const bool ok = (x >> 62) != 0 && (y >> 62) != 0;
+      if (__all_sync(0xffffffffu, ok)) break;
+      __nanosleep(32);
+      if (!ok) { x = ld_vol64(&X[j]); if (Y) y = ld_vol64(&Y[j]); }
     }
     const uint32_t have_x = __ballot_sync(0xffffffffu, (x >> 63) != 0), have_y = __ballot_sync(0xffffffffu, (y >> 63) != 0);
     const unsigned Lx = have_x ? (unsigned)(__ffs(have_x) - 1) : 32u, Ly = have_y ? (unsigned)(__ffs(have_y) - 1) : 32u;
@@ -198,14 +200,22 @@ TI_D void cta_resolve(unsigned long long *X, unsigned long long *Y, uint32_t c, 
     const unsigned long long ix = __shfl_sync(0xffffffffu, x, Lx & 31), iy = __shfl_sync(0xffffffffu, y, Ly & 31);
     if (lane == 0) { lb[w].L[0] = Lx; lb[w].L[1] = Ly; lb[w].s[0] = s0; lb[w].s[1] = s1; lb[w].s[2] = s2; lb[w].s[3] = s3; lb[w].inc[0] = ix; lb[w].inc[1] = iy; }
     __syncthreads();
-    for (unsigned k = 0; k < (unsigned)kWarps; ++k) {       // warp k looked at nearer chunks than warp k+1
+    // combine the warps' partial results (warp k looked at nearer chunks than warp k+1): lane k takes warp k's,
+    // every warp does the same few collectives instead of every thread walking the list
+    {
+      const bool in = lane < (unsigned)kWarps;
+      const LbWarp *q = lb + (in ? lane : 0);
+      const uint32_t hx = __ballot_sync(0xffffffffu, in && q->L[0] < 32), hy = __ballot_sync(0xffffffffu, in && q->L[1] < 32);
+      const unsigned kx = hx ? (unsigned)(__ffs(hx) - 1) : 31u, ky = hy ? (unsigned)(__ffs(hy) - 1) : 31u;   // first warp that saw an inclusive prefix
       if (!found_x) {
-        excl[0] += lb[k].s[0]; excl[1] += lb[k].s[1];
-        if (lb[k].L[0] < 32) { excl[0] += lb[k].inc[0] & 0x7fffffffull; excl[1] += lb[k].inc[0] >> 31 & 0x7fffffffull; found_x = true; }
+        excl[0] += __reduce_add_sync(0xffffffffu, in && lane <= kx ? q->s[0] : 0u);
+        excl[1] += __reduce_add_sync(0xffffffffu, in && lane <= kx ? q->s[1] : 0u);
+        if (hx) { const unsigned long long inc = lb[kx].inc[0]; excl[0] += inc & 0x7fffffffull; excl[1] += inc >> 31 & 0x7fffffffull; found_x = true; }
       }
       if (!found_y) {
-        excl[2] += lb[k].s[2]; excl[3] += lb[k].s[3];
-        if (lb[k].L[1] < 32) { excl[2] += lb[k].inc[1] & 0x7fffffffull; excl[3] += lb[k].inc[1] >> 31 & 0x7fffffffull; found_y = true; }
+        excl[2] += __reduce_add_sync(0xffffffffu, in && lane <= ky ? q->s[2] : 0u);
+        excl[3] += __reduce_add_sync(0xffffffffu, in && lane <= ky ? q->s[3] : 0u);
+        if (hy) { const unsigned long long inc = lb[ky].inc[1]; excl[2] += inc & 0x7fffffffull; excl[3] += inc >> 31 & 0x7fffffffull; found_y = true; }
       }
     }
     if (found_x && found_y) break;  // (the next use of lb is behind other barriers)
