@@ -50,6 +50,15 @@ class View(C.Structure):
     ]
 
 
+class ViewCompact(C.Structure):
+    """ti_view_compact: 16 B descriptors instead of base+stride rows / dense transactions."""
+    _fields_ = [
+        ("text", C.c_void_p), ("inst", C.c_void_p), ("desc", C.c_void_p), ("rows_full", C.c_void_p), ("txn_off", C.c_void_p),
+        ("txn", C.c_void_p), ("tb", C.c_void_p), ("warp", C.c_void_p), ("counts", Counts), ("n_full", C.c_uint64),
+        ("n_txn_stored", C.c_uint64),
+    ]
+
+
 class DevView(C.Structure):
     _fields_ = [
         ("text", C.c_void_p), ("inst", C.c_void_p), ("addr_rows", C.c_void_p), ("txn_off", C.c_void_p),
@@ -102,6 +111,7 @@ SYMBOLS = [
     "ti_kernel_dev_view", "ti_kernel_counters", "ti_counters_add", "ti_counters_finalize", "ti_kernel_timing",
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
     "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local", "ti_counters_derive", "ti_kernel_path_stats",
+    "ti_kernel_decode_streamed_compact", "ti_expand_row", "ti_expand_txns",
 ]
 
 
@@ -153,6 +163,9 @@ def load_library(path=None):
         "ti_kernel_coalesce_local": (C.c_int, [V, P(LocalMap), V, S, V, S, V, P(S)]),
         "ti_counters_derive": (C.c_int, [V, P(DerivedStats)]),
         "ti_kernel_path_stats": (C.c_int, [V, P(C.c_uint32 * 4)]),
+        "ti_kernel_decode_streamed_compact": (C.c_int, [V, S, P(ViewCompact)]),
+        "ti_expand_row": (None, [P(ViewCompact), U64, V]),
+        "ti_expand_txns": (C.c_uint32, [P(ViewCompact), U64, V]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -171,5 +184,5 @@ def np_view(ptr, dtype, n, shape=None):
     return a.reshape(shape) if shape else a
 
 
-__all__ = ["load_library", "NoAllocIO", "RegroupStats", "DerivedStats", "LocalMap", "TI_LOCAL_GENERIC_START", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "DevView", "Command", "TraceIngestError", "np_view",
+__all__ = ["load_library", "NoAllocIO", "RegroupStats", "DerivedStats", "LocalMap", "TI_LOCAL_GENERIC_START", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "ViewCompact", "DevView", "Command", "TraceIngestError", "np_view",
            "SYMBOLS", "EF", "R"]

@@ -40,6 +40,47 @@ class Decoded:
         return bytes(self.text[int(r["opc_off"]):int(r["opc_off"]) + int(r["opcode_len"])])
 
 
+class DecodedCompact:
+    """Host view of ti_view_compact: descriptors instead of base+stride rows and dense transactions;
+    expand_rows() / expand_txns() give what the full view holds (the library's own host expansion)."""
+
+    def __init__(self, lib, view, text_len):
+        n = view.counts
+        self._lib, self._view = lib, view
+        self.counts = {f: getattr(n, f) for f, _ in _ffi.Counts._fields_}
+        self.n_full, self.n_txn_stored = view.n_full, view.n_txn_stored
+        self.inst = _ffi.np_view(view.inst, R.INST, n.n_inst)
+        self.desc = _ffi.np_view(view.desc, R.MEM_DESC, n.n_mem)
+        self.rows_full = _ffi.np_view(view.rows_full, "<u8", view.n_full * 32, shape=(view.n_full, 32))
+        self.txn_off = _ffi.np_view(view.txn_off, "<u4", n.n_mem + 1)
+        self.txn = _ffi.np_view(view.txn, R.TXN, view.n_txn_stored)
+        self.tb = _ffi.np_view(view.tb, R.TB, n.n_tb)
+        self.warp = _ffi.np_view(view.warp, R.WARP, n.n_warp)
+        self.text = _ffi.np_view(view.text, "u1", text_len) if view.text else None
+        self.counters = None
+        self.d2h_bytes = (32 * len(self.inst) + 16 * len(self.desc) + 256 * len(self.rows_full) + 4 * len(self.txn_off) +
+                          32 * len(self.txn) + 32 * len(self.tb) + 16 * len(self.warp))
+
+    def expand_rows(self, lo=0, hi=None):
+        """ti_expand_row for memory instructions [lo, hi)."""
+        hi = len(self.desc) if hi is None else hi
+        out = np.zeros((hi - lo, 32), dtype="<u8")
+        for r in range(lo, hi):
+            self._lib.ti_expand_row(C.byref(self._view), r, out[r - lo].ctypes.data)
+        return out
+
+    def expand_txns(self, lo=0, hi=None):
+        """ti_expand_txns for memory instructions [lo, hi): (records, CSR offsets)."""
+        hi = len(self.desc) if hi is None else hi
+        buf = np.zeros(64, dtype=R.TXN)
+        parts, off = [], [0]
+        for r in range(lo, hi):
+            n = self._lib.ti_expand_txns(C.byref(self._view), r, buf.ctypes.data)
+            parts.append(buf[:n].copy())
+            off.append(off[-1] + n)
+        return (np.concatenate(parts) if parts else np.zeros(0, dtype=R.TXN)), np.asarray(off, dtype=np.uint32)
+
+
 class KernelTrace:
     """kernel_trace_t (trace_parser.h:81-102) plus the device-side decode state."""
 
@@ -136,6 +177,16 @@ class KernelTrace:
         d.power = pw[0]
         self._decoded = d
         self._next_tb = 0
+        return d
+
+    def run_streamed_compact(self, shard_bytes=0):
+        """ti_kernel_decode_streamed_compact: the pipelined host -> host path with compact results."""
+        view = _ffi.ViewCompact()
+        self._p._ck(self._p.lib.ti_kernel_decode_streamed_compact(self._h, shard_bytes, C.byref(view)))
+        d = DecodedCompact(self._p.lib, view, self.body_len)
+        cnt = np.zeros(1, dtype=R.COUNTERS)
+        self._p._ck(self._p.lib.ti_kernel_counters(self._h, cnt.ctypes.data))
+        d.counters = cnt[0]
         return d
 
     def coalesce_local(self, local_map, issues):

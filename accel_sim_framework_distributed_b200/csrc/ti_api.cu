@@ -16,6 +16,7 @@
 
 #include "ti_internal.h"
 #include "ti_kernels.cuh"
+#include "ti_compact.cuh"
 
 // the merged ISA table (generated from the reference's ISA_Def headers)
 #define TI_ISA_BEGIN static const struct IsaRow { const char *name; uint8_t id[5]; uint8_t cat[5]; } kIsaRows[] = {
@@ -101,7 +102,7 @@ static void stream_state_free(ti_stream_state *ss);
 struct ti_kernel {
   ti_ctx *ctx = nullptr;
   ti_stream_state *streams = nullptr;   // ti_kernel_decode_streamed: streams, events, two device buffer sets
-  bool streamed = false;
+  bool streamed = false, compact = false;   // the last decode went through the pipelined path / left compact results
   ti_kernel_hdr hdr;
   int col = -1;
   const char *h_body = nullptr;   // host body (owned pinned file image or borrowed)
@@ -113,7 +114,7 @@ struct ti_kernel {
   bool uploaded = false, decoded = false, synced = false, retried = false;
   DevBuf inst, rows, txn_off, txn, tb, warp, chains, globals, counters;
   uint64_t cap_inst = 0, cap_mem = 0, cap_txn = 0, cap_tb = 0, cap_warp = 0;
-  HostBuf h_inst, h_rows, h_txn_off, h_txn, h_tb, h_warp, h_small;
+  HostBuf h_inst, h_rows, h_txn_off, h_txn, h_tb, h_warp, h_small, h_desc;
   ti_counts counts;
   ti_counters host_counters;
   float decode_ms = 0;
@@ -269,7 +270,7 @@ void ti_kernel_close(ti_kernel *k) {
   stream_state_free(k->streams);
   DevBuf *d[] = {&k->d_text, &k->inst, &k->rows, &k->txn_off, &k->txn, &k->tb, &k->warp, &k->chains, &k->globals, &k->counters};
   for (DevBuf *b : d) b->release();
-  HostBuf *h[] = {&k->h_file, &k->h_inst, &k->h_rows, &k->h_txn_off, &k->h_txn, &k->h_tb, &k->h_warp, &k->h_small};
+  HostBuf *h[] = {&k->h_file, &k->h_inst, &k->h_rows, &k->h_txn_off, &k->h_txn, &k->h_tb, &k->h_warp, &k->h_small, &k->h_desc};
   for (HostBuf *b : h) b->release();
   delete k;
 }
@@ -279,7 +280,7 @@ ti_status ti_kernel_upload(ti_kernel *k, size_t begin, size_t end) {
   if (!k || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
   CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
   if (end - begin > 0xfffffff0ull) { ti::set_error("shard of %zu bytes: cut it with ti_plan_shards", end - begin); return TI_ERR_TOO_LARGE; }
-  k->decoded = k->synced = k->retried = k->streamed = false;
+  k->decoded = k->synced = k->retried = k->streamed = k->compact = false;
   if (k->d_borrowed) {
     if (begin & 15) { ti::set_error("device-resident shards must start 16-byte aligned"); return TI_ERR_INVALID_ARG; }
     k->sh_begin = begin; k->sh_len = end - begin; k->uploaded = true;
@@ -353,6 +354,7 @@ ti_status ti_kernel_sync(ti_kernel *k, ti_counts *counts) {
 ti_status ti_kernel_fetch(ti_kernel *k, ti_view *v) {
   if (!k || !v) return TI_ERR_INVALID_ARG;
   if (!k->synced) { ti::set_error("ti_kernel_fetch before a successful ti_kernel_sync"); return TI_ERR_STATE; }
+  if (k->compact) { ti::set_error("ti_kernel_fetch after a compact decode: the view was returned by ti_kernel_decode_streamed_compact"); return TI_ERR_STATE; }
   CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
   if (k->streamed) {  // ti_kernel_decode_streamed already brought everything to the host
     v->text = k->h_body;
@@ -516,6 +518,7 @@ namespace {
 
 struct StreamSet {
   DevBuf text, inst, rows, txn_off, txn, tb, warp, chains, globals, counters;
+  DevBuf desc, rows_c, txn_c, txn_off_c, part;   // compact results only
   HostBuf small;                           // Globals + ti_counters of the shard
   cudaEvent_t ev_h2d = nullptr, ev_dec = nullptr, ev_d2h = nullptr, t0 = nullptr, t1 = nullptr;
 };
@@ -555,7 +558,7 @@ struct ti_stream_state : StreamState {};
 static void stream_state_free(ti_stream_state *ss) {
   if (!ss) return;
   for (StreamSet &t : ss->set) {
-    DevBuf *d[] = {&t.text, &t.inst, &t.rows, &t.txn_off, &t.txn, &t.tb, &t.warp, &t.chains, &t.globals, &t.counters};
+    DevBuf *d[] = {&t.text, &t.inst, &t.rows, &t.txn_off, &t.txn, &t.tb, &t.warp, &t.chains, &t.globals, &t.counters, &t.desc, &t.rows_c, &t.txn_c, &t.txn_off_c, &t.part};
     for (DevBuf *b : d) b->release();
     t.small.release();
     cudaEvent_t *e[] = {&t.ev_h2d, &t.ev_dec, &t.ev_d2h, &t.t0, &t.t1};
@@ -566,8 +569,9 @@ static void stream_state_free(ti_stream_state *ss) {
   delete ss;
 }
 
-extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes, ti_view *v) {
-  if (!k || !v) return TI_ERR_INVALID_ARG;
+static ti_status decode_streamed_impl(ti_kernel *k, size_t shard_bytes, ti_view *v, ti_view_compact *vc) {
+  const bool compact = vc != nullptr;
+  if (!k || (!v && !vc)) return TI_ERR_INVALID_ARG;
   if (!k->h_body && k->body_len) { ti::set_error("ti_kernel_decode_streamed needs a host-resident body"); return TI_ERR_STATE; }
   if (k->body_len > 0xfffffff0ull) { ti::set_error("body of %zu bytes: opcode offsets are 32 bit", k->body_len); return TI_ERR_TOO_LARGE; }
   CK(cudaSetDevice(k->ctx->cfg.device));   // allocations and launches below belong to the context's device
@@ -621,7 +625,15 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     if ((st = t.chains.ensure(ti::chain_bytes(max_chunks))) != TI_OK) return st;
     if ((st = t.globals.ensure(sizeof(ti::Globals))) != TI_OK) return st;
     if ((st = t.counters.ensure(sizeof(ti_counters))) != TI_OK) return st;
-    if ((st = t.small.ensure(sizeof(ti::Globals) + sizeof(ti_counters))) != TI_OK) return st;
+    if ((st = t.small.ensure(sizeof(ti::Globals) + sizeof(ti_counters) + 16)) != TI_OK) return st;
+    if (compact) {
+      const uint32_t max_blocks = (uint32_t)((cap_mem + ti::kCpBlock - 1) / ti::kCpBlock);
+      if ((st = t.desc.ensure(cap_mem * sizeof(ti_mem_desc))) != TI_OK) return st;
+      if ((st = t.rows_c.ensure(cap_mem * 256)) != TI_OK) return st;
+      if ((st = t.txn_c.ensure(cap_txn * sizeof(ti_txn_rec))) != TI_OK) return st;
+      if ((st = t.txn_off_c.ensure((cap_mem + 1) * 4)) != TI_OK) return st;
+      if ((st = t.part.ensure(((size_t)2 * max_blocks + 2) * 4)) != TI_OK) return st;
+    }
   }
 
   cudaStream_t s_c = c->stream, s_up = ss->s_h2d, s_dn = ss->s_d2h;
@@ -634,7 +646,7 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     return TI_OK;
   };
 
-  uint64_t T_inst = 0, T_mem = 0, T_txn = 0, T_tb = 0, T_warp = 0;
+  uint64_t T_inst = 0, T_mem = 0, T_txn = 0, T_tb = 0, T_warp = 0, T_full = 0, T_keep = 0;
   ti_counters total;
   memset(&total, 0, sizeof total);
   uint32_t flags = 0, first_err = 0xffffffffu;
@@ -658,7 +670,8 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     P.warp = (ti_warp_rec *)t.warp.p; P.cap_warp = cap_warp;
     set_chains(P, t.chains.p, n_chunks);
     P.g = (ti::Globals *)t.globals.p; P.counters = (unsigned long long *)t.counters.p;
-    P.off_inst = T_inst; P.off_mem = T_mem; P.off_txn = T_txn; P.off_warp = T_warp; P.off_text = cuts[i];
+    P.off_inst = T_inst; P.off_mem = T_mem; P.off_txn = compact ? 0 : T_txn; P.off_warp = T_warp; P.off_text = cuts[i];
+    P.desc = compact ? (ti_mem_desc *)t.desc.p : nullptr;
 
     CK(cudaStreamWaitEvent(s_c, t.ev_h2d, 0));
     if (i >= 2) CK(cudaStreamWaitEvent(s_c, t.ev_d2h, 0));    // D2H(i-2) has drained this set's outputs
@@ -679,11 +692,36 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
 #endif
       CK(cudaGetLastError());
     }
+    uint32_t cp_blocks = 0;
+    if (compact && !n_chunks) CK(cudaMemsetAsync(t.txn_off_c.p, 0, 4, s_c));   // (an empty body: one CSR sentinel)
+    if (compact && n_chunks) {   // gather what still has to travel (ti_compact.cuh); n_mem is read on the device
+      ti::CompactParams C;
+      memset(&C, 0, sizeof C);
+      cp_blocks = (uint32_t)((cap_mem + ti::kCpBlock - 1) / ti::kCpBlock);
+      C.desc = (ti_mem_desc *)t.desc.p; C.txn_off = (const uint32_t *)t.txn_off.p; C.rows = (const uint64_t *)t.rows.p;
+      C.txn = (const ti_txn_rec *)t.txn.p; C.counters = (const unsigned long long *)t.counters.p; C.cap_mem = cap_mem;
+      C.off_txn_full = 0; C.rows_c = (uint64_t *)t.rows_c.p; C.txn_c = (ti_txn_rec *)t.txn_c.p; C.txn_off_c = (uint32_t *)t.txn_off_c.p;
+      C.cap_rows_c = cap_mem; C.cap_txn_c = cap_txn; C.part = (uint32_t *)t.part.p; C.n_blocks = cp_blocks;
+      C.off_full = T_full; C.off_txn_c = T_keep;
+#ifdef TI_EMU
+      emu::launch(dim3(cp_blocks), dim3(ti::kCpBlock), 8192, [=]() { ti::cp_count_kernel(C); });
+      emu::launch(dim3(1), dim3(ti::kCpBlock), 8192, [=]() { ti::cp_scan_kernel(C); });
+      emu::launch(dim3(cp_blocks), dim3(ti::kCpBlock), 8192, [=]() { ti::cp_gather_kernel(C); });
+#else
+      ti::cp_count_kernel<<<cp_blocks, ti::kCpBlock, 0, s_c>>>(C);
+      ti::cp_scan_kernel<<<1, ti::kCpBlock, 0, s_c>>>(C);
+      ti::cp_gather_kernel<<<cp_blocks, ti::kCpBlock, 0, s_c>>>(C);
+#endif
+      CK(cudaGetLastError());
+    }
     CK(cudaEventRecord(t.t1, s_c));
     ti::Globals *g = (ti::Globals *)t.small.p;
     ti_counters *hc = (ti_counters *)((char *)t.small.p + sizeof(ti::Globals));
+    uint32_t *hkeep = (uint32_t *)((char *)t.small.p + sizeof(ti::Globals) + sizeof(ti_counters));   // rows / transactions the compact pass kept
+    hkeep[0] = hkeep[1] = 0;
     CK(cudaMemcpyAsync(g, t.globals.p, sizeof(ti::Globals), cudaMemcpyDeviceToHost, s_c));
     CK(cudaMemcpyAsync(hc, t.counters.p, sizeof(ti_counters), cudaMemcpyDeviceToHost, s_c));
+    if (cp_blocks) CK(cudaMemcpyAsync(hkeep, (uint32_t *)t.part.p + 2 * (size_t)cp_blocks, 8, cudaMemcpyDeviceToHost, s_c));
     CK(cudaEventRecord(t.ev_dec, s_c));
     if (i + 2 < n_sh && (st = h2d(i + 2)) != TI_OK) return st;  // queued behind ev_dec of this set
     CK(cudaEventSynchronize(t.ev_dec));                         // the shard's counts are on the host now
@@ -695,10 +733,13 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     if (g->error_flags && first_err == 0xffffffffu) first_err = g->first_error_off + (uint32_t)cuts[i];   // shards come in file order: the first one wins
     // host arrays: grow when the running totals no longer fit (first shard: extrapolate)
     const double scale = 1.15 * (double)k->body_len / (double)std::max<size_t>(1, cuts[i + 1]);
+    const uint64_t add_rows = compact ? hkeep[0] : hc->n_mem, add_txn = compact ? hkeep[1] : hc->n_txn;   // what travels
+    const uint64_t at_rows = compact ? T_full : T_mem, at_txn = compact ? T_keep : T_txn;
     struct { HostBuf *b; uint64_t have, add; size_t elt; } need[] = {
-        {&k->h_inst, T_inst, hc->n_inst, sizeof(ti_inst_rec)}, {&k->h_rows, T_mem, hc->n_mem, 256},
-        {&k->h_txn_off, T_mem, hc->n_mem + 1, 4},               {&k->h_txn, T_txn, hc->n_txn, sizeof(ti_txn_rec)},
-        {&k->h_tb, T_tb, hc->n_tb, sizeof(ti_tb_rec)},          {&k->h_warp, T_warp, hc->n_warp, sizeof(ti_warp_rec)}};
+        {&k->h_inst, T_inst, hc->n_inst, sizeof(ti_inst_rec)}, {&k->h_rows, at_rows, add_rows, 256},
+        {&k->h_txn_off, T_mem, hc->n_mem + 1, 4},               {&k->h_txn, at_txn, add_txn, sizeof(ti_txn_rec)},
+        {&k->h_tb, T_tb, hc->n_tb, sizeof(ti_tb_rec)},          {&k->h_warp, T_warp, hc->n_warp, sizeof(ti_warp_rec)},
+        {&k->h_desc, compact ? T_mem : 0, compact ? hc->n_mem : 0, sizeof(ti_mem_desc)}};
     for (auto &nd : need) {
       const size_t want = (size_t)(nd.have + nd.add) * nd.elt;
       if (want <= nd.b->bytes) continue;
@@ -716,13 +757,15 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
       return TI_OK;
     };
     if ((st = down(k->h_inst, T_inst, t.inst, hc->n_inst, sizeof(ti_inst_rec))) != TI_OK) return st;
-    if ((st = down(k->h_rows, T_mem, t.rows, hc->n_mem, 256)) != TI_OK) return st;
-    if ((st = down(k->h_txn_off, T_mem, t.txn_off, hc->n_mem + 1, 4)) != TI_OK) return st;
-    if ((st = down(k->h_txn, T_txn, t.txn, hc->n_txn, sizeof(ti_txn_rec))) != TI_OK) return st;
+    if ((st = down(k->h_rows, at_rows, compact ? t.rows_c : t.rows, add_rows, 256)) != TI_OK) return st;
+    if ((st = down(k->h_txn_off, T_mem, compact ? t.txn_off_c : t.txn_off, hc->n_mem + 1, 4)) != TI_OK) return st;
+    if ((st = down(k->h_txn, at_txn, compact ? t.txn_c : t.txn, add_txn, sizeof(ti_txn_rec))) != TI_OK) return st;
+    if (compact && (st = down(k->h_desc, T_mem, t.desc, hc->n_mem, sizeof(ti_mem_desc))) != TI_OK) return st;
     if ((st = down(k->h_tb, T_tb, t.tb, hc->n_tb, sizeof(ti_tb_rec))) != TI_OK) return st;
     if ((st = down(k->h_warp, T_warp, t.warp, hc->n_warp, sizeof(ti_warp_rec))) != TI_OK) return st;
     CK(cudaEventRecord(t.ev_d2h, s_dn));
     T_inst += hc->n_inst; T_mem += hc->n_mem; T_txn += hc->n_txn; T_tb += hc->n_tb; T_warp += hc->n_warp;
+    T_full += hkeep[0]; T_keep += hkeep[1];
     ti_counters_add(&total, hc);
   }
   CK(cudaStreamSynchronize(s_dn));
@@ -733,7 +776,16 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
     if ((st = ti_kernel_upload(k, 0, k->body_len)) != TI_OK) return st;
     if ((st = ti_kernel_decode(k)) != TI_OK) return st;
     if ((st = ti_kernel_sync(k, NULL)) != TI_OK) return st;
-    return ti_kernel_fetch(k, v);
+    if (!compact) return ti_kernel_fetch(k, v);
+    // compact caller: hand the full arrays out under trivial descriptors (every row kept, every transaction stored)
+    ti_view fv;
+    if ((st = ti_kernel_fetch(k, &fv)) != TI_OK) return st;
+    if ((st = k->h_desc.ensure((size_t)(fv.counts.n_mem + 1) * sizeof(ti_mem_desc))) != TI_OK) return st;
+    ti_mem_desc *hd = (ti_mem_desc *)k->h_desc.p;
+    for (uint64_t r = 0; r < fv.counts.n_mem; ++r) { hd[r].base = r; hd[r].stride = 0; hd[r].meta = TI_DESC_FULL_ROW; }
+    vc->text = fv.text; vc->inst = fv.inst; vc->desc = hd; vc->rows_full = fv.addr_rows; vc->txn_off = fv.txn_off; vc->txn = fv.txn;
+    vc->tb = fv.tb; vc->warp = fv.warp; vc->counts = fv.counts; vc->n_full = fv.counts.n_mem; vc->n_txn_stored = fv.counts.n_txn;
+    return TI_OK;
   }
   if (T_inst > 0x7ffffffeull || T_txn > 0xfffffffeull) { ti::set_error("more than 2^31 records in one kernel file"); return TI_ERR_TOO_LARGE; }
   total.n_inst = T_inst; total.n_mem = T_mem; total.n_txn = T_txn; total.n_tb = T_tb; total.n_warp = T_warp;
@@ -747,8 +799,22 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
   k->counts.first_error_line_off = first_err == 0xffffffffu ? 0 : first_err;
   k->sh_begin = 0; k->sh_len = k->body_len;
   k->decode_ms = ms_sum;
-  k->synced = flags == 0; k->decoded = true; k->streamed = true;   // as ti_kernel_sync: nothing to fetch after a grammar error
+  k->synced = flags == 0; k->decoded = true; k->streamed = true; k->compact = false;   // as ti_kernel_sync: nothing to fetch after a grammar error
   if (flags) { ti::set_error("trace text outside the tracer grammar: flags 0x%x near body offset %u", flags, k->counts.first_error_line_off); return TI_ERR_PARSE; }
+  if (compact) {
+    k->compact = true;   // ti_kernel_fetch hands out full arrays: there are none after a compact decode
+    vc->text = k->h_body;
+    vc->inst = (const ti_inst_rec *)k->h_inst.p;
+    vc->desc = (const ti_mem_desc *)k->h_desc.p;
+    vc->rows_full = (const uint64_t *)k->h_rows.p;
+    vc->txn_off = (const uint32_t *)k->h_txn_off.p;
+    vc->txn = (const ti_txn_rec *)k->h_txn.p;
+    vc->tb = (const ti_tb_rec *)k->h_tb.p;
+    vc->warp = (const ti_warp_rec *)k->h_warp.p;
+    vc->counts = k->counts;
+    vc->n_full = T_full; vc->n_txn_stored = T_keep;
+    return TI_OK;
+  }
   v->text = k->h_body;
   v->inst = (const ti_inst_rec *)k->h_inst.p;
   v->addr_rows = (const uint64_t *)k->h_rows.p;
@@ -758,6 +824,16 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
   v->warp = (const ti_warp_rec *)k->h_warp.p;
   v->counts = k->counts;
   return TI_OK;
+}
+
+extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes, ti_view *v) {
+  if (!v) return TI_ERR_INVALID_ARG;
+  return decode_streamed_impl(k, shard_bytes, v, nullptr);
+}
+
+extern "C" ti_status ti_kernel_decode_streamed_compact(ti_kernel *k, size_t shard_bytes, ti_view_compact *vc) {
+  if (!vc) return TI_ERR_INVALID_ARG;
+  return decode_streamed_impl(k, shard_bytes, nullptr, vc);
 }
 
 // =====================================================================================

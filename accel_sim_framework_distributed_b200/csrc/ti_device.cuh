@@ -132,6 +132,8 @@ struct DecodeParams {
   uint64_t *rows;     uint64_t cap_mem;
   uint32_t *txn_off;
   ti_txn_rec *txn;    uint64_t cap_txn;
+  ti_mem_desc *desc;  // compact mode (else null): one 16 B descriptor per memory instruction [cap_mem]; rows of base+stride
+                      // instructions and transactions of dense ones are then NOT written (they are closed forms of it)
   ti_tb_rec *tb;      uint64_t cap_tb;
   ti_warp_rec *warp;  uint64_t cap_warp;
   // value offsets: what the preceding shards of the same kernel file produced, so that

@@ -163,6 +163,61 @@ ti_status ti_plan_shards(const char *body, size_t len, int n, size_t *cuts) {
   return TI_OK;
 }
 
+// ---- host-side expansion of the compact view (ti_view_compact): the same closed forms the kernel uses.
+// Row: trace_parser.cc:86-105 (base_stride_decompress: base + i * stride over the mask's first run, 0 elsewhere).
+// Dense transactions: abstract_hardware_model.cc:509-586 on a contiguous, aligned run + :694-748 (size reduction).
+void ti_expand_row(const ti_view_compact *v, uint64_t mem_idx, uint64_t out[32]) {
+  const ti_mem_desc &d = v->desc[mem_idx];
+  if (d.meta & TI_DESC_FULL_ROW) { memcpy(out, v->rows_full + d.base * 32, 256); return; }
+  const unsigned first = d.meta & 31, n = d.meta >> 5 & 63;
+  for (unsigned l = 0; l < 32; ++l)
+    out[l] = l - first < n ? d.base + (uint64_t)(int64_t)d.stride * (uint64_t)(l - first) : 0;
+}
+
+uint32_t ti_expand_txns(const ti_view_compact *v, uint64_t mem_idx, ti_txn_rec *out) {
+  const ti_mem_desc &d = v->desc[mem_idx];
+  if (!(d.meta & TI_DESC_DENSE)) {
+    const uint32_t b = v->txn_off[mem_idx], e = v->txn_off[mem_idx + 1];
+    if (e > b) memcpy(out, v->txn + b, (size_t)(e - b) * sizeof(ti_txn_rec));
+    return e - b;
+  }
+  const unsigned first = d.meta & 31, n = d.meta >> 5 & 63, ds = 1u << (d.meta >> 11 & 7), seg = 32u << (d.meta >> 14 & 3), wr = d.meta >> 16 & 1;
+  const unsigned sh = d.meta >> 11 & 7;
+  const uint64_t segmask = ~(uint64_t)(seg - 1), end = d.base + (uint64_t)n * ds;
+  uint32_t k = 0;
+  for (uint64_t S = d.base & segmask; S < end; S += seg, ++k) {
+    const uint64_t lo = S > d.base ? S : d.base, hi = S + seg < end ? S + seg : end;
+    const unsigned i0 = (unsigned)((lo - d.base) >> sh), i1 = (unsigned)((hi - d.base) >> sh);   // lanes [i0, i1) of the run
+    const unsigned p0 = (unsigned)(lo & 127), p1 = p0 + (unsigned)(hi - lo);                   // bytes [p0, p1) of the 128 B line
+    ti_txn_rec r;
+    memset(&r, 0, sizeof r);
+    r.lane_mask = (i1 - i0 == 32 ? 0xffffffffu : ((1u << (i1 - i0)) - 1)) << (first + i0);
+    unsigned chunks = 0;
+    for (unsigned w = 0; w < 4; ++w) {
+      const unsigned a = p0 > 32 * w ? p0 : 32 * w, b = p1 < 32 * w + 32 ? p1 : 32 * w + 32;
+      if (b > a) { r.byte_mask[w] = (b - a == 32 ? 0xffffffffu : ((1u << (b - a)) - 1)) << (a - 32 * w); chunks |= 1u << w; }
+    }
+    // memory_coalescing_arch_reduce_and_send (abstract_hardware_model.cc:694-748)
+    uint64_t addr = S;
+    unsigned size = seg, h = 0;
+    if (seg == 128) {
+      const bool l2 = chunks & 3, h2 = chunks & 12;
+      if (l2 && !h2) { size = 64; h = chunks & 3; }
+      else if (!l2 && h2) { addr += 64; size = 64; h = (chunks >> 2) & 3; }
+    } else if (seg == 64) {
+      h = (addr % 128 == 0) ? (chunks & 3) : ((chunks >> 2) & 3);
+    }
+    if (size == 64) {
+      const bool l1 = h & 1, h1 = h & 2;
+      if (l1 && !h1) size = 32;
+      else if (!l1 && h1) { addr += 32; size = 32; }
+    }
+    r.addr = addr; r.size = (uint8_t)size; r.sector_mask = (uint8_t)chunks; r.type = wr ? 4 : 0; r.is_write = (uint8_t)wr;
+    out[k] = r;
+  }
+  return k;
+}
+
 void ti_counters_add(ti_counters *acc, const ti_counters *x) {
   uint64_t *a = (uint64_t *)acc;
   const uint64_t *b = (const uint64_t *)x;

@@ -129,9 +129,21 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     const uint8_t *txn_cnt = smem + oTxnCnt + par * align16(kItems) + wid * kWarpInst;
     const uint8_t *m_io = smem + oMIo + par * align16(kItems) + wid * kWarpInst;
     const uint64_t wmem = base_mem + pw.mem0, wtxn = base_txn + pw.txn0, winst = base_inst + pw.inst0;
+    // compact mode: the 16 B descriptor stands for the row (and, for a dense progression, for the transactions)
+    if (P.desc) {
+      for (uint32_t fo = lane; fo < pw.n_notes; fo += 32) {
+        const StrideNote nt = wnotes[fo];
+        const uint64_t row = wmem + ((nt.meta >> 18 & 0x3ff) - wid * kWarpInst);
+        if (!(nt.meta >> 28 & 1) && row < P.cap_mem) {
+          ti_mem_desc dd;
+          dd.base = nt.base; dd.stride = nt.stride; dd.meta = nt.meta & 0x3ffffu;
+          P.desc[row] = dd;
+        }
+      }
+    }
     // address rows of the base+stride instructions: half a warp per row, two addresses (16 B) per lane,
     // so every store instruction covers two whole 256 B rows
-    for (uint32_t f0 = 0; f0 < pw.n_notes; f0 += 2) {
+    for (uint32_t f0 = 0; f0 < (P.desc ? 0u : (uint32_t)pw.n_notes); f0 += 2) {
       const uint32_t fo = f0 + (lane >> 4);
       if (fo < pw.n_notes) {
         const StrideNote nt = wnotes[fo];
@@ -168,7 +180,8 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         d.base = nt.base; d.stride = nt.stride; d.first = meta & 31; d.n = meta >> 5 & 63;
         const unsigned ds = 1u << (meta >> 11 & 7), seg = 32u << (meta >> 14 & 3), is_write = meta >> 16 & 1;
         if (meta >> 17 & 1) {
-          for (unsigned k = sub; k < room; k += 4) txn_store(P.txn + at + k, dense_txn(d, ds, seg, is_write ? 4u : 0u, is_write, k));
+          if (!P.desc)
+            for (unsigned k = sub; k < room; k += 4) txn_store(P.txn + at + k, dense_txn(d, ds, seg, is_write ? 4u : 0u, is_write, k));
         } else if (sub == 0) stride_emit(d, ds, seg, is_write ? 4u : 0u, is_write, P.txn + at, room);
       } else {                                         // warp path: staged in the pool
         const uint4 *src = reinterpret_cast<const uint4 *>(stage + slot);
@@ -522,6 +535,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         fl = __reduce_or_sync(kFull, fl);              // a bad token is seen by one lane only: make it warp-uniform
         const uint64_t row = base_mem + mo;
         if (row < P.cap_mem) P.rows[row * 32 + lane] = addr;
+        if (P.desc && lane == 0 && row < P.cap_mem) { ti_mem_desc dd; dd.base = 0; dd.stride = 0; dd.meta = TI_DESC_FULL_ROW; P.desc[row] = dd; }
         if (resolve) {                                 // trace_driven.cc:331-351
           const uint64_t a0 = __shfl_sync(kFull, addr, __ffs(mask) - 1);
           unsigned space = SPACE_GLOBAL, cache_op = CACHE_ALL;

@@ -15,6 +15,7 @@ TB = np.dtype([
     ("text_off", "<u8"), ("x", "<i4"), ("y", "<i4"), ("z", "<i4"),
     ("first_warp", "<u4"), ("first_inst", "<u4"), ("line_len", "<u4"),
 ])
+MEM_DESC = np.dtype([("base", "<u8"), ("stride", "<i4"), ("meta", "<u4")])   # ti_mem_desc
 WARP = np.dtype([("warp_id", "<u4"), ("n_insts", "<u4"), ("first_inst", "<u4"), ("reserved", "<u4")])
 COUNTERS = np.dtype([
     ("hist", "<u8", (18, 33)), ("op_count", "<u8", (32,)), ("space_lanes", "<u8", (16, 2)),

@@ -196,3 +196,45 @@ def run_rare_paths(tp, tmp_path):
     # [3] more base+stride instructions in a chunk than descriptors fit
     lines = ["%x 1 0 LDG 0 4 1 0x%x 4 0" % (16 * i, 0x7F3000000000 + 256 * i) for i in range(1500)]   # ~30 bytes: > 256 per chunk
     assert decode(edge_cases.image([(0, 0, 0, [lines, []])]), "notes_full")[3] > 0
+
+
+def check_compact(k, shard_bytes=0):
+    """The compact view (ti_kernel_decode_streamed_compact), expanded on the host by the library's own
+    ti_expand_row / ti_expand_txns, is bit-identical to the full view of the same kernel file."""
+    whole = k.run()
+    want = {n: getattr(whole, n).copy() for n in ("inst", "rows", "txn_off", "txn", "tb", "warp")}
+    wc = np.zeros(1, dtype=T.COUNTERS)
+    wc[0] = whole.counters
+    c = k.run_streamed_compact(shard_bytes)
+    for n in ("inst", "tb", "warp"):
+        assert np.array_equal(getattr(c, n), want[n]), n
+    assert len(c.desc) == len(want["rows"]) and c.counts["n_txn"] == len(want["txn"])
+    assert np.array_equal(c.expand_rows(), want["rows"]), "rows"
+    txn, off = c.expand_txns()
+    assert np.array_equal(off, want["txn_off"]), "txn_off"
+    assert np.array_equal(txn, want["txn"]), "txn"
+    for f in T.COUNTERS.names:
+        if f != "reserved":
+            assert np.array_equal(c.counters[f], wc[0][f]), f
+    return c
+
+
+def run_compact(tp, tmp_path, shard_bytes=0, **gen):
+    path = os.path.join(str(tmp_path), "kernel-1.traceg")
+    harness.generate(path, **gen)
+    k = tp.parse_kernel_info(path)
+    c = check_compact(k, shard_bytes)
+    tp.kernel_finalizer(k)
+    return c
+
+
+def run_compact_golden(tp, name):
+    over = edge_cases.VALID.get(name, (None, {}))[1]
+    p, own = parser_with(tp, over)
+    try:
+        k = p.parse_kernel_info(os.path.join(GOLDEN, name + ".traceg"))
+        check_compact(k)
+        p.kernel_finalizer(k)
+    finally:
+        if own:
+            p.close()

@@ -85,3 +85,17 @@ def test_emu_streamed_empty_tail_shards_and_error_offset(emu_parser, tmp_path):
     assert np.array_equal(d.txn_off, want_off)
     assert int(d.txn_off[-1]) == len(d.txn)
     emu_parser.kernel_finalizer(k)
+
+
+@pytest.mark.parametrize("name", parity_cases.golden_names())
+def test_emu_compact_golden(emu_parser, name):
+    parity_cases.run_compact_golden(emu_parser, name)
+
+
+def test_emu_compact_generated(emu_parser, tmp_path):
+    """Compact results expand to the full ones: a base+stride corpus (nothing but descriptors travels) and
+    the mixed one (rows and transactions of list / delta instructions are kept), over several shards."""
+    c = parity_cases.run_compact(emu_parser, tmp_path, profile=2, seed=5, n_tb=12, insts_per_warp=25)
+    assert c.n_full <= 0.02 * len(c.desc) and c.n_txn_stored <= 0.02 * c.counts["n_txn"]   # (a warp with more than 32 such lines sends the rest down the warp path)
+    c = parity_cases.run_compact(emu_parser, tmp_path, shard_bytes=30000, profile=5, seed=6, n_tb=24, insts_per_warp=8, block_threads=96)
+    assert 0 < c.n_full < len(c.desc) and 0 < c.n_txn_stored < c.counts["n_txn"]

@@ -229,6 +229,54 @@ def test_config2_full_size_vs_reference(cuda_parser, tmp_path):
     print("full-size differential test: %d slices, oracle=%s, %.1f s" % (len(paths), kind, time.time() - t_start))
 
 
+@pytest.mark.parametrize("name", [n for n in parity_cases.golden_names() if n.startswith("edge_")])
+def test_compact_golden(cuda_parser, name):
+    """The stride quirks of trace_parser.cc:86-105 (zero after the first run, u64 wrap, empty masks ...) through the
+    compact view: expanded == full."""
+    parity_cases.run_compact_golden(cuda_parser, name)
+
+
+def test_compact_expands_to_full(cuda_parser, tmp_path):
+    c = parity_cases.run_compact(cuda_parser, tmp_path, shard_bytes=1 << 20, profile=2, seed=2, n_tb=400, insts_per_warp=25)
+    assert c.n_full <= 0.02 * len(c.desc) and c.d2h_bytes < 0.3 * (32 * len(c.inst) + 260 * len(c.desc) + 32 * c.counts["n_txn"])
+    c = parity_cases.run_compact(cuda_parser, tmp_path, shard_bytes=300000, profile=5, seed=31, n_tb=300, insts_per_warp=10, block_threads=128)
+    assert 0 < c.n_full < len(c.desc)
+    parity_cases.run_compact(cuda_parser, tmp_path, profile=3, seed=3, n_tb=100, insts_per_warp=12)
+
+
+def test_compact_config2_full_size(cuda_parser):
+    """BASELINE config 2 at full size through the compact path: vectorised expansion of every descriptor equals the
+    full view's rows, the records are identical, and less than a quarter of the bytes travel."""
+    img = harness.generate_bytes(profile=2, seed=2, n_tb=100000, insts_per_warp=25)
+    hdr = cuda_parser.parse_header(img[:4096])
+    body = img[hdr.body_offset:]
+    k = cuda_parser.open_buffer(body, hdr)
+    full = k.run_streamed(64 << 20)
+    inst, rows, txn, off = full.inst.copy(), full.rows.copy(), full.txn.copy(), full.txn_off.copy()
+    c = k.run_streamed_compact(64 << 20)
+    assert np.array_equal(c.inst, inst)
+    d = c.desc
+    is_full = (d["meta"] >> 29 & 1).astype(bool)
+    first, n = (d["meta"] & 31).astype(np.int64), (d["meta"] >> 5 & 63).astype(np.int64)
+    lanes = np.arange(32, dtype=np.int64)[None, :] - first[:, None]
+    for lo in range(0, len(d), 1 << 20):      # in slabs: the whole expansion would need several GB of temporaries
+        hi = min(len(d), lo + (1 << 20))
+        want = rows[lo:hi]
+        got = np.where((lanes[lo:hi] >= 0) & (lanes[lo:hi] < n[lo:hi, None]),
+                       d["base"][lo:hi, None] + (d["stride"][lo:hi, None].astype(np.int64) * lanes[lo:hi]).astype(np.uint64), np.uint64(0))
+        f = is_full[lo:hi]
+        if f.any():
+            got[f] = c.rows_full[d["base"][lo:hi][f].astype(np.int64)]
+        assert np.array_equal(got, want), lo
+    # transactions: the library's own expansion on a sample, the stored ones in full
+    rng = np.random.default_rng(1)
+    for r in rng.integers(0, len(d), 2000):
+        t, o = c.expand_txns(int(r), int(r) + 1)
+        assert np.array_equal(t, txn[off[r]:off[r + 1]]), r
+    assert c.d2h_bytes < 0.25 * (32 * len(inst) + 256 * len(rows) + 4 * len(off) + 32 * len(txn))
+    cuda_parser.kernel_finalizer(k)
+
+
 @pytest.mark.parametrize("shard_bytes", [1 << 20, 300000])
 def test_streamed_host_path(cuda_parser, tmp_path, shard_bytes):
     parity_cases.run_streamed(cuda_parser, tmp_path, shard_bytes, profile=5, seed=31, n_tb=800, insts_per_warp=10, block_threads=128)
