@@ -690,13 +690,19 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
   flush_counters(cnt, P.counters);
 }
 
-// Framing check over the finished warp-header table (the reference would trip an
-// assert or index past a vector, trace_parser.cc:435-443): every "insts = n" must be
-// followed by exactly n instruction lines.
+// Framing and structure check over the finished tables (the reference would trip an assert or index past
+// a vector, trace_parser.cc:414-443): every "insts = n" must be followed by exactly n instruction lines,
+// every "warp = w" by its "insts = n", and "#BEGIN_TB" / "thread block" / "#END_TB" lines must pair up.
+// The second check is also made on the host by the entry points that bring the counters there; here it
+// reaches the callers that read only the device-side status block (ti_decode_noalloc).
 __global__ void ti_check_kernel(const ti_warp_rec *warp, uint64_t cap_warp, const unsigned long long *counters, Globals *g, uint64_t off_inst = 0) {
   const uint64_t n_warp = counters[kCntNInst + 4], n_inst = counters[kCntNInst + 0] + off_inst;
-  if (n_warp > cap_warp) return;  // the table overflowed: the host decodes again with exact capacities
   const uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (uint64_t)gridDim.x * blockDim.x;
+  if (t0 == 0) {
+    const uint64_t n_tb = counters[kCntNInst + 3], n_begin = counters[kCntNInst + 5], n_end = counters[kCntNInst + 6], n_insts_lines = counters[kCntNInst + 9];
+    if (n_begin != n_end || n_begin != n_tb || n_insts_lines != n_warp) atomicOr(&g->error_flags, (uint32_t)TI_EF_BAD_STRUCTURE);
+  }
+  if (n_warp > cap_warp) return;  // the table overflowed: the host decodes again with exact capacities
   if (t0 == 0 && (n_warp ? warp[0].first_inst != off_inst : n_inst != off_inst)) atomicOr(&g->error_flags, (uint32_t)TI_EF_FRAMING);
   for (uint64_t k = t0; k < n_warp; k += stride) {
     const uint64_t next = k + 1 < n_warp ? warp[k + 1].first_inst : n_inst;
