@@ -112,7 +112,7 @@ struct ti_kernel {
   DevBuf d_text;
   size_t sh_begin = 0, sh_len = 0;
   bool uploaded = false, decoded = false, synced = false, retried = false;
-  DevBuf inst, rows, txn_off, txn, tb, warp, chains, globals, counters;
+  DevBuf inst, rows, txn_off, txn, tb, warp, chains, globals, counters, counters_sum;
   uint64_t cap_inst = 0, cap_mem = 0, cap_txn = 0, cap_tb = 0, cap_warp = 0;
   HostBuf h_inst, h_rows, h_txn_off, h_txn, h_tb, h_warp, h_small, h_desc;
   ti_counts counts;
@@ -268,7 +268,7 @@ void ti_kernel_close(ti_kernel *k) {
   if (!k) return;
   cudaStreamSynchronize(k->ctx->stream);
   stream_state_free(k->streams);
-  DevBuf *d[] = {&k->d_text, &k->inst, &k->rows, &k->txn_off, &k->txn, &k->tb, &k->warp, &k->chains, &k->globals, &k->counters};
+  DevBuf *d[] = {&k->d_text, &k->inst, &k->rows, &k->txn_off, &k->txn, &k->tb, &k->warp, &k->chains, &k->globals, &k->counters, &k->counters_sum};
   for (DevBuf *b : d) b->release();
   HostBuf *h[] = {&k->h_file, &k->h_inst, &k->h_rows, &k->h_txn_off, &k->h_txn, &k->h_tb, &k->h_warp, &k->h_small, &k->h_desc};
   for (HostBuf *b : h) b->release();
@@ -945,6 +945,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
   return TI_OK;
 }
 
+#include "ti_nccl.inc"
 #include "ti_regroup_api.inc"
 #include "ti_local_api.inc"
 

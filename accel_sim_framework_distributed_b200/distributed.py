@@ -88,3 +88,38 @@ def finalize(parser, counters):
     pw = np.zeros(1, dtype=R.POWER)
     parser._ck(parser.lib.ti_counters_finalize(parser.ctx, cnt.ctypes.data, pw.ctypes.data))
     return pw[0]
+
+
+class NcclCounters:
+    """The same reduction through the library's own C-ABI collective (ti_allreduce_counters): an NCCL
+    communicator created from a unique id that rank 0 draws and torch.distributed carries to the other ranks
+    (any transport would do: it is 128 bytes), then one device-to-device ncclAllReduce per call."""
+
+    def __init__(self, parser, group=None):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        self._p, self._C = parser, C
+        world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        rank = dist.get_rank(group) if world > 1 else 0
+        uid = np.zeros(128, dtype=np.uint8)
+        if rank == 0:
+            parser._ck(parser.lib.ti_nccl_unique_id(uid.ctypes.data))
+        if world > 1:
+            t = torch.from_numpy(uid).cuda()
+            dist.broadcast(t, src=0, group=group)
+            uid = t.cpu().numpy()
+        self.comm = C.c_void_p()
+        parser._ck(parser.lib.ti_nccl_comm_create(parser.ctx, uid.ctypes.data, world, rank, C.byref(self.comm)))
+        self.world, self.rank = world, rank
+
+    def allreduce(self, kernel):
+        """Sum of the last decode's counter block of `kernel` (a KernelTrace) over the ranks -> numpy record."""
+        out = np.zeros(1, dtype=R.COUNTERS)
+        self._p._ck(self._p.lib.ti_allreduce_counters(kernel._h, self.comm, None, out.ctypes.data))
+        return out[0]
+
+    def close(self):
+        if self.comm:
+            self._p.lib.ti_nccl_comm_destroy(self.comm)
+            self.comm = None
