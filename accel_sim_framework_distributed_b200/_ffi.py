@@ -112,7 +112,7 @@ SYMBOLS = [
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
     "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local", "ti_counters_derive", "ti_kernel_path_stats",
     "ti_kernel_decode_streamed_compact", "ti_expand_row", "ti_expand_txns",
-    "ti_nccl_unique_id", "ti_nccl_comm_create", "ti_nccl_comm_destroy", "ti_allreduce_counters",
+    "ti_kernel_decode_window_compact", "ti_kernel_host_body", "ti_nccl_unique_id", "ti_nccl_comm_create", "ti_nccl_comm_destroy", "ti_allreduce_counters",
 ]
 
 
@@ -165,6 +165,8 @@ def load_library(path=None):
         "ti_counters_derive": (C.c_int, [V, P(DerivedStats)]),
         "ti_kernel_path_stats": (C.c_int, [V, P(C.c_uint32 * 4)]),
         "ti_kernel_decode_streamed_compact": (C.c_int, [V, S, P(ViewCompact)]),
+        "ti_kernel_decode_window_compact": (C.c_int, [V, S, S, S, P(ViewCompact)]),
+        "ti_kernel_host_body": (C.c_int, [V, P(V), P(S)]),
         "ti_expand_row": (None, [P(ViewCompact), U64, V]),
         "ti_expand_txns": (C.c_uint32, [P(ViewCompact), U64, V]),
         "ti_nccl_unique_id": (C.c_int, [V]),

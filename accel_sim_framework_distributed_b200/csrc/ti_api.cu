@@ -10,6 +10,12 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#ifndef TI_EMU
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#endif
 
 #include <algorithm>
 #include <vector>
@@ -107,7 +113,9 @@ struct ti_kernel {
   int col = -1;
   const char *h_body = nullptr;   // host body (owned pinned file image or borrowed)
   size_t body_len = 0;
-  HostBuf h_file;                 // owns the file image for ti_kernel_open_file
+  HostBuf h_file;                 // owns the file image for ti_kernel_open_file (when it could not be mapped)
+  void *map_base = nullptr;       // ... or the read-only mapping of the file (pages come and go with the page cache)
+  size_t map_len = 0;
   const uint8_t *d_borrowed = nullptr;
   DevBuf d_text;
   size_t sh_begin = 0, sh_len = 0;
@@ -223,25 +231,52 @@ static ti_status new_kernel(ti_ctx *ctx, const ti_kernel_hdr *hdr, ti_kernel **o
 ti_status ti_kernel_open_file(ti_ctx *ctx, const char *path, ti_kernel_hdr *hdr, ti_kernel **out) {
   if (!ctx || !path || !out) return TI_ERR_INVALID_ARG;
   CK(cudaSetDevice(ctx->cfg.device));
-  FILE *f = fopen(path, "rb");
-  if (!f) { ti::set_error("Unable to open file: %s", path); return TI_ERR_IO; }  // trace_parser.cc:306-309
-  fseek(f, 0, SEEK_END);
-  const long n = ftell(f);
-  fseek(f, 0, SEEK_SET);
+  // The file is mapped read-only rather than read into pinned memory: a caller that walks it window by window
+  // (ti_kernel_decode_window_compact, the C++ drop-in) then never holds more than a window of it.
+  void *map = nullptr;
+  size_t n = 0;
   HostBuf img;
-  ti_status st = img.ensure((size_t)n + 16);
-  if (st != TI_OK) { fclose(f); return st; }
-  const size_t got = n ? fread(img.p, 1, (size_t)n, f) : 0;
-  fclose(f);
-  if (got != (size_t)n) { img.release(); ti::set_error("short read on %s", path); return TI_ERR_IO; }
+#ifndef TI_EMU
+  {
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) { ti::set_error("Unable to open file: %s", path); return TI_ERR_IO; }  // trace_parser.cc:306-309
+    struct stat sb;
+    if (fstat(fd, &sb) == 0 && sb.st_size > 0) {
+      n = (size_t)sb.st_size;
+      map = mmap(nullptr, n, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (map == MAP_FAILED) map = nullptr;
+    }
+    close(fd);
+  }
+#endif
+  if (!map) {
+    FILE *f = fopen(path, "rb");
+    if (!f) { ti::set_error("Unable to open file: %s", path); return TI_ERR_IO; }  // trace_parser.cc:306-309
+    fseek(f, 0, SEEK_END);
+    n = (size_t)ftell(f);
+    fseek(f, 0, SEEK_SET);
+    ti_status st = img.ensure(n + 16);
+    if (st != TI_OK) { fclose(f); return st; }
+    const size_t got = n ? fread(img.p, 1, n, f) : 0;
+    fclose(f);
+    if (got != n) { img.release(); ti::set_error("short read on %s", path); return TI_ERR_IO; }
+  }
+  const char *base = map ? (const char *)map : (const char *)img.p;
   ti_kernel_hdr h;
-  ti_parse_kernel_header((const char *)img.p, (size_t)n, &h);
+  ti_parse_kernel_header(base, n, &h);
   if (hdr) *hdr = h;
-  st = new_kernel(ctx, &h, out);
-  if (st != TI_OK) { img.release(); return st; }
+  ti_status st = new_kernel(ctx, &h, out);
+  if (st != TI_OK) {
+    img.release();
+#ifndef TI_EMU
+    if (map) munmap(map, n);
+#endif
+    return st;
+  }
   (*out)->h_file = img;
-  (*out)->h_body = (const char *)img.p + h.body_offset;
-  (*out)->body_len = (size_t)n - h.body_offset;
+  (*out)->map_base = map; (*out)->map_len = n;
+  (*out)->h_body = base + h.body_offset;
+  (*out)->body_len = n - h.body_offset;
   return TI_OK;
 }
 
@@ -272,6 +307,9 @@ void ti_kernel_close(ti_kernel *k) {
   for (DevBuf *b : d) b->release();
   HostBuf *h[] = {&k->h_file, &k->h_inst, &k->h_rows, &k->h_txn_off, &k->h_txn, &k->h_tb, &k->h_warp, &k->h_small, &k->h_desc};
   for (HostBuf *b : h) b->release();
+#ifndef TI_EMU
+  if (k->map_base) munmap(k->map_base, k->map_len);
+#endif
   delete k;
 }
 
@@ -834,6 +872,25 @@ extern "C" ti_status ti_kernel_decode_streamed(ti_kernel *k, size_t shard_bytes,
 extern "C" ti_status ti_kernel_decode_streamed_compact(ti_kernel *k, size_t shard_bytes, ti_view_compact *vc) {
   if (!vc) return TI_ERR_INVALID_ARG;
   return decode_streamed_impl(k, shard_bytes, nullptr, vc);
+}
+
+extern "C" ti_status ti_kernel_host_body(ti_kernel *k, const char **body, size_t *len) {
+  if (!k || !body || !len) return TI_ERR_INVALID_ARG;
+  if (!k->h_body && k->body_len) { ti::set_error("the kernel object has no host-resident body"); return TI_ERR_STATE; }
+  *body = k->h_body; *len = k->body_len;
+  return TI_OK;
+}
+
+extern "C" ti_status ti_kernel_decode_window_compact(ti_kernel *k, size_t begin, size_t end, size_t shard_bytes, ti_view_compact *vc) {
+  if (!k || !vc || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
+  if (!k->h_body && k->body_len) { ti::set_error("ti_kernel_decode_window_compact needs a host-resident body"); return TI_ERR_STATE; }
+  // the window is decoded as a body of its own: every index and text offset in the view counts from `begin`
+  const char *body = k->h_body;
+  const size_t len = k->body_len;
+  k->h_body = body + begin; k->body_len = end - begin;
+  const ti_status st = decode_streamed_impl(k, shard_bytes, nullptr, vc);
+  k->h_body = body; k->body_len = len;
+  return st;
 }
 
 // =====================================================================================

@@ -267,6 +267,36 @@ def writer_side(tp, torch):
                          "algorithmic_bytes": "input read once + output written once"}}
 
 
+def shim_block(img, window_mb=256):
+    """SURVEY 8(d) "the shim's materialisation reported separately": one driver (oracle/tp_driver.cc, `time` mode) walks
+    every thread block of the corpus through trace_parser::get_next_threadblock_traces, once built against the reference's
+    own trace_parser.cc (oracle/_ref/tp_ref) and once against the drop-in over the CUDA library (oracle/_ref/tp_shim_cuda).
+    Wall seconds, instructions per second and peak resident set of both; single host thread each."""
+    import harness
+    ref = os.path.join(harness.ROOT, "oracle", "_ref", "tp_ref")
+    shim = os.path.join(harness.ROOT, "oracle", "_ref", "tp_shim_cuda")
+    if not (os.access(ref, os.X_OK) and os.access(shim, os.X_OK)):
+        return {"unavailable": "oracle/_ref/tp_ref or tp_shim_cuda not built"}
+    out = {"window_mb": window_mb, "how": "tp_driver time: parse_kernel_info + get_next_threadblock_traces over all thread blocks, parser stdout discarded"}
+    with tempfile.TemporaryDirectory() as tmp:
+        img.tofile(os.path.join(tmp, "kernel-1.traceg"))
+        open(os.path.join(tmp, "kernelslist.g"), "w").write("kernel-1.traceg\n")
+        for name, exe in (("drop_in_b200", shim), ("reference", ref)):
+            r = subprocess.run([exe, "time", "./kernelslist.g"], cwd=tmp, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True,
+                               env=dict(os.environ, TI_SHIM_WINDOW_MB=str(window_mb)))
+            try:
+                d = json.loads(r.stderr.strip().splitlines()[-1])
+                d["warp_insts_per_s"] = d["n_inst"] / d["seconds"]
+                d["GB_per_s"] = len(img) / d["seconds"] / 1e9
+                out[name] = d
+            except Exception:
+                out[name] = {"failed": r.returncode, "stderr": r.stderr[-300:]}
+    if "seconds" in out.get("drop_in_b200", {}) and "seconds" in out.get("reference", {}):
+        out["speedup"] = out["reference"]["seconds"] / out["drop_in_b200"]["seconds"]
+        out["same_checksum"] = out["reference"]["checksum"] == out["drop_in_b200"]["checksum"]
+    return out
+
+
 def bench_b200(args):
     import torch
     import harness
@@ -487,6 +517,7 @@ def bench_b200(args):
                                     "sample": "first %.0f MB (whole thread blocks) of the same corpus, 1 process, parse+convert+coalesce, stdout discarded" % (nbytes / 1e6)}
         if world == 1 and not args.no_extras and wl == "config2":
             line["writer_side"] = writer_side(tp, torch)
+            line["shim"] = shim_block(imgs[0])
         print(json.dumps(line))
     nccl.close()
     for k in kds + kes:

@@ -8,8 +8,53 @@
 
 #include "trace_parser.h"
 
+// `tp_driver time <kernelslist.g>`: the same walk without printing -- wall seconds of parse_kernel_info +
+// get_next_threadblock_traces over every thread block of every kernel, instructions seen, peak resident set.
+// (stdout of the parser itself, its header and "thread block" echo lines, is left to the caller to discard.)
+static int time_mode(const char *list) {
+  const auto t0 = std::chrono::steady_clock::now();
+  trace_parser tracer(list);
+  unsigned long long n_inst = 0, n_mem = 0, n_tb_seen = 0, sum = 0;
+  for (const trace_command &c : tracer.parse_commandlist_file()) {
+    if (c.m_type != command_type::kernel_launch) continue;
+    kernel_trace_t *k = tracer.parse_kernel_info(c.command_string);
+    const unsigned n_warps = (k->tb_dim_x * k->tb_dim_y * k->tb_dim_z + 31) / 32;
+    std::vector<std::vector<inst_trace_t>> warps(n_warps);
+    std::vector<std::vector<inst_trace_t> *> ptrs;
+    for (auto &w : warps) ptrs.push_back(&w);
+    const unsigned long long n_tb = (unsigned long long)k->grid_dim_x * k->grid_dim_y * k->grid_dim_z;
+    for (unsigned long long tb = 0; tb < n_tb; ++tb) {
+      tracer.get_next_threadblock_traces(ptrs, k->trace_verion, k->ifs);
+      ++n_tb_seen;
+      for (auto &w : warps)
+        for (const inst_trace_t &t : w) {
+          ++n_inst;
+          sum += t.m_pc + t.mask + t.opcode.size();
+          if (t.memadd_info) { ++n_mem; sum += t.memadd_info->addrs[0] + t.memadd_info->addrs[31]; }
+        }
+    }
+    tracer.kernel_finalizer(k);
+  }
+  const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  // VmHWM of this address space (ru_maxrss would carry the parent's high-water mark across fork + exec)
+  double hwm_mb = 0, anon_mb = 0;
+  if (FILE *f = fopen("/proc/self/status", "r")) {
+    char line[256];
+    while (fgets(line, sizeof line, f)) {
+      long kb;
+      if (sscanf(line, "VmHWM: %ld kB", &kb) == 1) hwm_mb = kb / 1024.0;
+      if (sscanf(line, "RssAnon: %ld kB", &kb) == 1) anon_mb = kb / 1024.0;
+    }
+    fclose(f);
+  }
+  fprintf(stderr, "{\"seconds\": %.3f, \"n_inst\": %llu, \"n_mem\": %llu, \"n_tb\": %llu, \"checksum\": %llu, \"peak_rss_mb\": %.1f, \"rss_anon_at_end_mb\": %.1f}\n", sec,
+          n_inst, n_mem, n_tb_seen, sum, hwm_mb, anon_mb);
+  return 0;
+}
+
 int main(int argc, char **argv) {
   if (argc < 2) return 2;
+  if (argc > 2 && !strcmp(argv[1], "time")) return time_mode(argv[2]);
   trace_parser tracer(argv[1]);
   std::vector<trace_command> cmds = tracer.parse_commandlist_file();
   for (const trace_command &c : cmds) {

@@ -5,9 +5,14 @@
 // :306-309), abort() where the reference asserts, ownership of kernel_trace_t / ifs
 // (:301-302, :379-385), thread blocks handed out in file order (:387-447).
 //
-// What changes: the first get_next_threadblock_traces call of a kernel decodes the
-// whole kernel file on the GPU (one fused launch); every call then only copies one
-// thread block of finished records into the caller's vectors.
+// What changes: get_next_threadblock_traces decodes the kernel file on the GPU one
+// WINDOW at a time (256 MiB of text by default, TI_SHIM_WINDOW_MB; a window starts at
+// "#BEGIN_TB") and every call then only copies one thread block of finished records
+// into the caller's vectors.  The next window is decoded when the current one is used up
+// and reuses its buffers, so the drop-in holds one window of results whatever the size
+// of the file -- the reference holds one thread block per call (trace_parser.cc:387-447).
+// The results travel in compact form (ti_view_compact): the 256-byte address row of a
+// base+stride instruction is expanded here, on hand-out, from its 16-byte descriptor.
 #include <bits/stdc++.h>
 
 #include "trace_parser.h"
@@ -35,10 +40,21 @@ bool all_digits(const std::string &s, size_t from) {
 
 struct KernelState {
   ti_kernel *k = nullptr;
-  ti_view view;
-  bool decoded = false;
-  uint64_t next_tb = 0;
+  size_t body_len = 0;
+  const char *body = nullptr;          // host body (the library's mapping of the file)
+  ti_view_compact view;                // the current window
+  std::vector<size_t> cuts;            // window boundaries in the body, all at "#BEGIN_TB"
+  size_t next_window = 0;
+  bool planned = false;
+  uint64_t next_tb = 0;                // next thread block of the current window
 };
+
+size_t window_bytes() {
+  if (const char *b = getenv("TI_SHIM_WINDOW_BYTES")) { const long long v = atoll(b); if (v > 0) return (size_t)v; }   // (tests: tiny windows)
+  const char *e = getenv("TI_SHIM_WINDOW_MB");
+  const long mb = e ? atol(e) : 256;
+  return (size_t)(mb > 0 ? mb : 256) << 20;
+}
 
 }  // namespace
 
@@ -250,14 +266,26 @@ void trace_parser::get_next_threadblock_traces(std::vector<std::vector<inst_trac
   auto it = m->kernels.find(ifs);
   if (it == m->kernels.end()) return;
   KernelState &s = it->second;
-  if (!s.decoded) {
-    // the whole kernel file in one fused launch; later calls only copy records out
-    ti_status st = ti_kernel_decode_streamed(s.k, 0, &s.view);  // copies and kernel overlapped
+  if (!s.planned) {
+    ti_status st = ti_kernel_host_body(s.k, &s.body, &s.body_len);
     if (st != TI_OK) die("get_next_threadblock_traces", st);
-    s.decoded = true;
+    const int n_win = (int)std::max<size_t>(1, (s.body_len + window_bytes() - 1) / window_bytes());
+    s.cuts.assign(n_win + 1, 0);
+    st = ti_plan_shards(s.body, s.body_len, n_win, s.cuts.data());
+    if (st != TI_OK) die("ti_plan_shards", st);
+    s.planned = true;
+    memset(&s.view, 0, sizeof s.view);
   }
-  const ti_view &v = s.view;
-  if (s.next_tb >= v.counts.n_tb) return;  // the reference's loop ends at EOF with nothing filled
+  while (s.next_tb >= s.view.counts.n_tb) {   // the window is used up (or none decoded yet): next non-empty one
+    if (s.next_window + 1 >= s.cuts.size()) return;  // the reference's loop ends at EOF with nothing filled
+    const size_t b = s.cuts[s.next_window], e = s.cuts[s.next_window + 1];
+    ++s.next_window;
+    if (e == b) continue;
+    ti_status st = ti_kernel_decode_window_compact(s.k, b, e, 0, &s.view);  // copies and kernel overlapped inside
+    if (st != TI_OK) die("get_next_threadblock_traces", st);
+    s.next_tb = 0;
+  }
+  const ti_view_compact &v = s.view;
   const uint64_t k = s.next_tb++;
   const ti_tb_rec &tb = v.tb[k];
   std::cout << std::string(v.text + tb.text_off, tb.line_len) << std::endl;  // trace_parser.cc:427
@@ -279,7 +307,7 @@ void trace_parser::get_next_threadblock_traces(std::vector<std::vector<inst_trac
       for (unsigned j = 0; j < t.reg_srcs_num; ++j) t.reg_src[j] = r.src[j];
       if (TI_HAS_MEM(&r)) {
         t.memadd_info = new inst_memadd_info_t();
-        memcpy(t.memadd_info->addrs, v.addr_rows + (size_t)r.mem_idx * 32, sizeof t.memadd_info->addrs);
+        ti_expand_row(&v, r.mem_idx, (uint64_t *)t.memadd_info->addrs);   // 16 B descriptor -> inst_memadd_info_t::addrs
         // inst_trace_t keeps the opcode-derived width (the LDC override belongs to the next stage)
         t.memadd_info->width = (int32_t)t.get_datawidth_from_opcode(t.get_opcode_tokens());
       }

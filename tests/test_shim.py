@@ -50,6 +50,27 @@ def test_shim_matches_reference_cuda(tmp_path):
     _run_both(harness.CUDA_LIB, str(tmp_path))
 
 
+def _windowed(lib_path, tmp):
+    """A kernel file walked in many small windows (TI_SHIM_WINDOW_BYTES) gives the reference's output byte for byte."""
+    harness.generate(os.path.join(tmp, "kernel-1.traceg"), profile=5, seed=61, n_tb=40, insts_per_warp=9, block_threads=96)
+    open(os.path.join(tmp, "kernelslist.g"), "w").write("kernel-1.traceg\n")
+    shim = _build_shim(lib_path, os.path.join(tmp, "tp_shim"))
+    a = subprocess.run([TP_REF, "./kernelslist.g"], cwd=tmp, capture_output=True)
+    for window in ("20000", "7000"):
+        b = subprocess.run([shim, "./kernelslist.g"], cwd=tmp, capture_output=True, env=dict(os.environ, TI_SHIM_WINDOW_BYTES=window))
+        assert a.returncode == 0 and b.returncode == 0, (a.returncode, b.returncode, b.stderr[-500:])
+        assert a.stdout == b.stdout, window
+
+
+def test_shim_windowed_emulated(tmp_path):
+    _windowed(harness.emu_library(), str(tmp_path))
+
+
+@pytest.mark.gpu
+def test_shim_windowed_cuda(tmp_path):
+    _windowed(harness.CUDA_LIB, str(tmp_path))
+
+
 def test_shim_unopenable_file_exits_1(tmp_path):
     """trace_parser.cc:224-227,306-309: message on stdout + exit(1)."""
     shim = _build_shim(harness.emu_library(), os.path.join(str(tmp_path), "tp_shim"))
