@@ -94,6 +94,11 @@ class DerivedStats(C.Structure):
     _fields_ = [("active_lane_distro", C.c_uint64 * 33), ("smem_bank_conflict", C.c_uint64), ("uncoalesced_gmem", C.c_uint64)]
 
 
+class PipelineStats(C.Structure):
+    _fields_ = [("regfile_reads", C.c_uint64), ("regfile_writes", C.c_uint64), ("non_rf_operands", C.c_uint64),
+                ("decoded_insn", C.c_uint64), ("int_decoded_insn", C.c_uint64), ("fp_decoded_insn", C.c_uint64)]
+
+
 class RegroupStats(C.Structure):
     _fields_ = [("n_lines", C.c_uint64), ("n_keys", C.c_uint64), ("out_bytes", C.c_uint64), ("n_tb_written", C.c_uint32),
                 ("n_tb_empty", C.c_uint32), ("n_warp_empty", C.c_uint32), ("device_ms", C.c_float)]
@@ -112,7 +117,7 @@ SYMBOLS = [
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
     "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local", "ti_counters_derive", "ti_kernel_path_stats",
     "ti_kernel_decode_streamed_compact", "ti_expand_row", "ti_expand_txns",
-    "ti_kernel_decode_window_compact", "ti_kernel_host_body", "ti_nccl_unique_id", "ti_nccl_comm_create", "ti_nccl_comm_destroy", "ti_allreduce_counters",
+    "ti_kernel_pipeline_stats", "ti_kernel_decode_window_compact", "ti_kernel_host_body", "ti_nccl_unique_id", "ti_nccl_comm_create", "ti_nccl_comm_destroy", "ti_allreduce_counters",
 ]
 
 
@@ -167,6 +172,7 @@ def load_library(path=None):
         "ti_kernel_decode_streamed_compact": (C.c_int, [V, S, P(ViewCompact)]),
         "ti_kernel_decode_window_compact": (C.c_int, [V, S, S, S, P(ViewCompact)]),
         "ti_kernel_host_body": (C.c_int, [V, P(V), P(S)]),
+        "ti_kernel_pipeline_stats": (C.c_int, [V, C.c_int, C.c_int, P(PipelineStats)]),
         "ti_expand_row": (None, [P(ViewCompact), U64, V]),
         "ti_expand_txns": (C.c_uint32, [P(ViewCompact), U64, V]),
         "ti_nccl_unique_id": (C.c_int, [V]),
@@ -191,5 +197,5 @@ def np_view(ptr, dtype, n, shape=None):
     return a.reshape(shape) if shape else a
 
 
-__all__ = ["load_library", "NoAllocIO", "RegroupStats", "DerivedStats", "LocalMap", "TI_LOCAL_GENERIC_START", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "ViewCompact", "DevView", "Command", "TraceIngestError", "np_view",
+__all__ = ["load_library", "NoAllocIO", "PipelineStats", "RegroupStats", "DerivedStats", "LocalMap", "TI_LOCAL_GENERIC_START", "TI_NOALLOC_MAX_TEXT", "KernelHdr", "Counts", "View", "ViewCompact", "DevView", "Command", "TraceIngestError", "np_view",
            "SYMBOLS", "EF", "R"]

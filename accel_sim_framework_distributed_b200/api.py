@@ -143,6 +143,12 @@ class KernelTrace:
         self._p._ck(self._p.lib.ti_kernel_path_stats(self._h, C.byref(out)))
         return tuple(out)
 
+    def pipeline_stats(self, clock_gated_reg_file=0, n_regfile_gating_group=4):
+        """ti_kernel_pipeline_stats of the last one-piece decode: register-file and decode counters."""
+        out = _ffi.PipelineStats()
+        self._p._ck(self._p.lib.ti_kernel_pipeline_stats(self._h, clock_gated_reg_file, n_regfile_gating_group, C.byref(out)))
+        return {f: getattr(out, f) for f, _ in _ffi.PipelineStats._fields_}
+
     def decode_ms(self):
         ms = C.c_float()
         self._p._ck(self._p.lib.ti_kernel_timing(self._h, C.byref(ms)))

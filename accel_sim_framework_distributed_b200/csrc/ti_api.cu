@@ -1003,6 +1003,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
 }
 
 #include "ti_nccl.inc"
+#include "ti_pstats.inc"
 #include "ti_regroup_api.inc"
 #include "ti_local_api.inc"
 

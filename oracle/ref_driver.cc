@@ -204,6 +204,17 @@ int main(int argc, char **argv) {
   std::vector<std::vector<inst_trace_t> *> ptrs;
   for (auto &w : warps) ptrs.push_back(&w);
 
+  // SURVEY 8 f3, the statistics of the timing model that are functions of the trace alone (restated counting rule over
+  // the REFERENCE's own trace_warp_inst_t fields: arch_reg.src / dst, oprnd_type, active mask):
+  //   register-file reads  (shader.cc:4313-4336, 4384-4402): one event per DISTINCT valid source register of an instruction,
+  //                        worth warp_size lanes, or the lanes of the gating groups that hold an active lane
+  //   register-file writes (shader.cc:4183-4232): one event per destination register (the trace has at most one)
+  //   non-RF operands      (shader.cc:4234-4255): num_operands - num_regs = 0 for every trace instruction (trace_driven.cc:225-226)
+  //   decoded instructions (shader.cc:887-916): a warp is fetched only with an empty ibuffer (shader.cc:968-970) and decode()
+  //                        takes two instructions, so the pairs are (2k, 2k+1) of the warp's stream; the second one is counted
+  //                        INT when the FIRST is INT_OP / UN_OP (pI1 is tested twice), else FP when it is FP_OP itself
+  unsigned long long ps_reads[2] = {0, 0}, ps_writes[2] = {0, 0}, ps_dec = 0, ps_int = 0, ps_fp = 0;   // [0] no gating, [1] gating groups of ps_group lanes
+  const unsigned ps_group = getenv("TI_RF_GATING_GROUP") ? (unsigned)atoi(getenv("TI_RF_GATING_GROUP")) : 4;
   ti_dump d;
   ti_oracle::counter_acc acc;
   d.txn_off.push_back(0);
@@ -235,6 +246,31 @@ int main(int argc, char **argv) {
         inst.parse_from_trace_struct(t, isa, &tconfig, kinfo);
         // shader_core_ctx::issue_warp -> warp_inst_t::issue (shader.cc:1030-1117)
         inst.issue(inst.get_active_mask(), w, 0, w, 0);
+        {
+          unsigned distinct = 0, n_dst = 0, gated = 0;
+          int seen[MAX_REG_OPERANDS];
+          for (unsigned op = 0; op < MAX_REG_OPERANDS; ++op) {
+            const int reg = inst.arch_reg.src[op];
+            bool fresh = reg >= 0;
+            for (unsigned j = 0; j < distinct; ++j) fresh = fresh && seen[j] != reg;
+            if (fresh) seen[distinct++] = reg;
+            if (inst.arch_reg.dst[op] >= 0) ++n_dst;
+          }
+          for (unsigned g0 = 0; g0 < 32; g0 += ps_group)
+            for (unsigned j = 0; j < ps_group; ++j)
+              if (inst.get_active_mask().test(g0 + j)) { gated += ps_group; break; }
+          ps_reads[0] += 32ull * distinct; ps_reads[1] += (unsigned long long)gated * distinct;
+          ps_writes[0] += 32ull * n_dst; ps_writes[1] += (unsigned long long)gated * n_dst;
+          ++ps_dec;
+          static int first_type = 0;                // oprnd_type of the pair's first instruction
+          const int ty = (int)inst.oprnd_type;      // UN_OP = -1, INT_OP = 0, FP_OP = 1
+          if (i % 2 == 0) {
+            first_type = ty;
+            if (ty == INT_OP || ty == UN_OP) ++ps_int; else if (ty == FP_OP) ++ps_fp;
+          } else {
+            if (first_type == INT_OP || first_type == UN_OP) ++ps_int; else if (ty == FP_OP) ++ps_fp;
+          }
+        }
         bool is_local = inst.space.get_type() == local_space;
         unsigned cycles = 0;
         if (stages >= 3 && (inst.is_load() || inst.is_store()) && !is_local) {
@@ -367,9 +403,11 @@ int main(int argc, char **argv) {
     if (nt) fwrite(local_txn.data(), sizeof(ti_txn_rec), nt, f);
     fclose(f);
   }
-  printf("{\"impl\":\"reference\",\"stages\":%d,\"seconds\":%.6f,\"n_inst\":%llu,\"n_tb\":%llu,\"n_txn\":%llu}\n",
+  printf("{\"impl\":\"reference\",\"stages\":%d,\"seconds\":%.6f,\"n_inst\":%llu,\"n_tb\":%llu,\"n_txn\":%llu,"
+         "\"pstats\":{\"gating_group\":%u,\"regfile_reads\":[%llu,%llu],\"regfile_writes\":[%llu,%llu],\"non_rf_operands\":0,"
+         "\"decoded_insn\":%llu,\"int_decoded_insn\":%llu,\"fp_decoded_insn\":%llu}}\n",
          stages, sec, (unsigned long long)n_inst_total, (unsigned long long)n_tb_total,
-         (unsigned long long)n_txn_total);
+         (unsigned long long)n_txn_total, ps_group, ps_reads[0], ps_reads[1], ps_writes[0], ps_writes[1], ps_dec, ps_int, ps_fp);
   parser.kernel_finalizer(kinfo);
   return 0;
 }

@@ -238,3 +238,28 @@ def run_compact_golden(tp, name):
     finally:
         if own:
             p.close()
+
+
+def run_pipeline_stats(tp, tmp_path, **gen):
+    """register-file read / write totals and the decode counters against the restated counting rule
+    applied to the REFERENCE's own trace_warp_inst_t fields (ref_oracle prints them in its summary line)."""
+    import json
+    import subprocess
+    if harness.oracle_kind() != "reference":
+        import pytest
+        pytest.skip("needs the reference-built oracle")
+    path = os.path.join(str(tmp_path), "kernel-1.traceg")
+    harness.generate(path, **gen)
+    k = tp.parse_kernel_info(path)
+    k.run()
+    for group in (4, 8):
+        r = subprocess.run([harness.REF_ORACLE, "time", path, "", "convert"], capture_output=True, text=True,
+                           env=dict(os.environ, TI_RF_GATING_GROUP=str(group)))
+        want = json.loads(r.stdout.strip().splitlines()[-1])["pstats"]
+        plain, gated = k.pipeline_stats(0, group), k.pipeline_stats(1, group)
+        for got, idx in ((plain, 0), (gated, 1)):
+            assert got["regfile_reads"] == want["regfile_reads"][idx] and got["regfile_writes"] == want["regfile_writes"][idx], (group, idx, got, want)
+            assert got["non_rf_operands"] == 0 == want["non_rf_operands"]
+            for f in ("decoded_insn", "int_decoded_insn", "fp_decoded_insn"):
+                assert got[f] == want[f], (f, got, want)
+    tp.kernel_finalizer(k)

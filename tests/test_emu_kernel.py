@@ -99,3 +99,7 @@ def test_emu_compact_generated(emu_parser, tmp_path):
     assert c.n_full <= 0.02 * len(c.desc) and c.n_txn_stored <= 0.02 * c.counts["n_txn"]   # (a warp with more than 32 such lines sends the rest down the warp path)
     c = parity_cases.run_compact(emu_parser, tmp_path, shard_bytes=30000, profile=5, seed=6, n_tb=24, insts_per_warp=8, block_threads=96)
     assert 0 < c.n_full < len(c.desc) and 0 < c.n_txn_stored < c.counts["n_txn"]
+
+
+def test_emu_pipeline_stats(emu_parser, tmp_path):
+    parity_cases.run_pipeline_stats(emu_parser, tmp_path, profile=5, seed=71, n_tb=20, insts_per_warp=11, block_threads=96)

@@ -282,5 +282,11 @@ def test_streamed_host_path(cuda_parser, tmp_path, shard_bytes):
     parity_cases.run_streamed(cuda_parser, tmp_path, shard_bytes, profile=5, seed=31, n_tb=800, insts_per_warp=10, block_threads=128)
 
 
+@pytest.mark.parametrize("profile,bv", [(5, 70), (5, 86), (2, 70), (1, 70)])
+def test_pipeline_stats(cuda_parser, tmp_path, profile, bv):
+    parity_cases.run_pipeline_stats(cuda_parser, tmp_path, profile=profile, seed=300 + profile + bv, n_tb=150, insts_per_warp=13,
+                                    block_threads=128, binary_version=bv)
+
+
 def test_rare_paths(cuda_parser, tmp_path):
     parity_cases.run_rare_paths(cuda_parser, tmp_path)   # more chunks than resident CTAs (444)
