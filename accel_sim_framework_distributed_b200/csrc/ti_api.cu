@@ -23,6 +23,7 @@
 #include "ti_internal.h"
 #include "ti_kernels.cuh"
 #include "ti_compact.cuh"
+#include "ti_compress.cuh"
 
 // the merged ISA table (generated from the reference's ISA_Def headers)
 #define TI_ISA_BEGIN static const struct IsaRow { const char *name; uint8_t id[5]; uint8_t cat[5]; } kIsaRows[] = {
@@ -91,10 +92,13 @@ int arch_column(unsigned v) {  // trace_driven.cc:100-118
 
 struct ti_regroup_state;
 static void regroup_state_free(ti_regroup_state *s);
+struct ti_compress_state;
+static void compress_state_free(ti_compress_state *w);
 
 struct ti_ctx {
   ti_config cfg;
   ti_regroup_state *rg = nullptr;   // workspace of ti_regroup_* (allocated on first use)
+  ti_compress_state *cmp = nullptr; // workspace of ti_compress_rows
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   ti::IsaSlot *d_isa[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -205,6 +209,7 @@ static ti_status ctx_init(ti_ctx *c, const ti_config *cfg) {
 void ti_ctx_destroy(ti_ctx *c) {
   if (!c) return;
   regroup_state_free(c->rg);
+  compress_state_free(c->cmp);
   for (auto &p : c->d_isa) if (p) cudaFree(p);
   if (c->d_spop) cudaFree(c->d_spop);
   if (c->ev0) cudaEventDestroy(c->ev0);
@@ -1004,6 +1009,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
 
 #include "ti_nccl.inc"
 #include "ti_pstats.inc"
+#include "ti_compress_api.inc"
 #include "ti_regroup_api.inc"
 #include "ti_local_api.inc"
 
