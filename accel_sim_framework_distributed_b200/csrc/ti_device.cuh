@@ -48,7 +48,7 @@ namespace ti {
 #define TI_THREADS 384
 #endif
 #ifndef TI_TXN_STAGE
-#define TI_TXN_STAGE 672
+#define TI_TXN_STAGE 608
 #endif
 #ifndef TI_TEXT_BUFS
 #define TI_TEXT_BUFS 1     // text buffers; the text is dead after P6b, so one buffer takes the prefetch of the next chunk too

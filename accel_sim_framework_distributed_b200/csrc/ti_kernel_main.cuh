@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
 
     // ---------------------------------------------------------------- S offsets of the warps inside the chunk; chains 0 / 1 / 2
     // (lane k takes warp k's totals; sums and the sums over the warps before this one by warp reductions)
-    uint32_t n_inst, n_sl, n_tb, n_warp, n_mem, n_txn_chunk, inst0, tb0, warp0, mem0, txn0;
+    uint32_t n_inst, n_sl, n_tb, n_warp, n_mem, n_txn_chunk, inst0, tb0, warp0, mem0, txn0, sl0;
     {
       const bool in = lane < (unsigned)kWarps, before = lane < wid;
       WarpTot t = ms->wt[in ? lane : 0];
@@ -420,13 +420,32 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       const uint32_t sa = __reduce_add_sync(kFull, a), sb = __reduce_add_sync(kFull, b), pa = __reduce_add_sync(kFull, before ? a : 0u), pb = __reduce_add_sync(kFull, before ? b : 0u);
       n_inst = sa & 0xffff; n_tb = sa >> 16; n_warp = sb & 0xffff; n_mem = sb >> 16;
       inst0 = pa & 0xffff; tb0 = pa >> 16; warp0 = pb & 0xffff; mem0 = pb >> 16;
-      n_sl = __reduce_add_sync(kFull, (uint32_t)t.n_sl);
+      n_sl = __reduce_add_sync(kFull, (uint32_t)t.n_sl); sl0 = __reduce_add_sync(kFull, before ? (uint32_t)t.n_sl : 0u);
       n_txn_chunk = __reduce_add_sync(kFull, t.n_txn); txn0 = __reduce_add_sync(kFull, before ? t.n_txn : 0u);
     }
     const uint32_t n_warp_path = ms->n_slowq;               // CTA-uniform
     if (lane == 0) { WarpPre q; q.inst0 = (uint16_t)inst0; q.mem0 = (uint16_t)mem0; q.n_mem = (uint16_t)mem_seen; q.n_notes = (uint16_t)n_notes_w; q.txn0 = txn0; ms->pw[par][wid] = q; }
     const unsigned long long aggA0 = chain_pack(n_inst, n_tb), aggA1 = chain_pack(n_warp, 0);
     if (tid == 0) { chain_publish(P.chain[0], chunk, aggA0); chain_publish(P.chain[1], chunk, aggA1); chain_publish(P.chain[2], chunk, chain_pack(n_mem, 0)); }
+
+    // the warps list their structural lines for the CTA-wide pass H (if the chunk's lines fit the list)
+    const bool sl_listed = n_sl <= (uint32_t)kSlList;          // CTA-uniform
+    if (sl_listed) {
+      uint32_t tb_seen = tb0, warp_seen = warp0;
+      for (uint32_t i0 = 0; i0 < n_sl_w; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool valid = i < n_sl_w;
+        const int o = valid ? wl_sl[i] : 0;
+        const unsigned c = valid ? text[o] : 0u;
+        const uint32_t tbb = __ballot_sync(kFull, c == 't'), wb = __ballot_sync(kFull, c == 'w');
+        const uint32_t ex_tb = tb_seen + __popc(tbb & lt), ex_w = warp_seen + __popc(wb & lt);
+        tb_seen += __popc(tbb); warp_seen += __popc(wb);
+        if (!valid) continue;
+        uint32_t lo = 0, hi = n_inst_w;              // instruction lines before this one = its rank in the warp's sorted line list
+        while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (wl_inst[mid] < o) lo = mid + 1; else hi = mid; }
+        reinterpret_cast<uint4 *>(smem + oSlList)[sl0 + i] = make_uint4((uint32_t)o, inst0 + lo, ex_tb, ex_w);
+      }
+    }
 
     // ---------------------------------------------------------------- F' the previous chunk's rows and transactions
     // (before anything of this chunk goes into the pool)
@@ -453,29 +472,20 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       __syncthreads();                                     // Misc::lb may be written again by the next resolve
     }
 
-    // ---------------------------------------------------------------- H structural lines of the warp's range
-    // "#BEGIN_TB" / "#END_TB" / "thread block = x,y,z" / "warp = w" + look-ahead "insts = n": a lane per line,
-    // ordinals of "thread block" and "warp" lines from ballots (the lanes hold the lines in file order)
+    // ---------------------------------------------------------------- H structural lines
+    // "#BEGIN_TB" / "#END_TB" / "thread block = x,y,z" / "warp = w" + look-ahead "insts = n".  There are few of them per
+    // warp range (a lane per line would leave most lanes idle through a long dependent chain), so the warps only listed
+    // them (above, Misc-side list `sllist`: offset, instruction lines before it, thread-block / warp ordinal) and the
+    // CTA takes the list a thread per line; a chunk with more of them than the list holds keeps them per warp.
     {
       ti_tb_rec *tb_out = late ? park_tb : P.tb + exA[1];
       ti_warp_rec *warp_out = late ? park_warp : P.warp + exA[2];
       const uint64_t tb_room = late ? ~0ull : (P.cap_tb > exA[1] ? P.cap_tb - exA[1] : 0);
       const uint64_t warp_room = late ? ~0ull : (P.cap_warp > exA[2] ? P.cap_warp - exA[2] : 0);
-      const uint64_t inst_base = (late ? 0 : exA[0] + P.off_inst) + inst0, warp_base = late ? 0 : exA[2] + P.off_warp;
-      uint32_t tb_seen = tb0, warp_seen = warp0;
-      for (uint32_t i0 = 0; i0 < n_sl_w; i0 += 32) {
-        const uint32_t i = i0 + lane;
-        const bool valid = i < n_sl_w;
-        const int o = valid ? wl_sl[i] : 0;
-        const unsigned c = valid ? text[o] : 0u;
-        const uint32_t tbb = __ballot_sync(kFull, c == 't'), wb = __ballot_sync(kFull, c == 'w');
-        const uint32_t ex_tb = tb_seen + __popc(tbb & lt), ex_w = warp_seen + __popc(wb & lt);
-        tb_seen += __popc(tbb); warp_seen += __popc(wb);
-        if (!valid) continue;
-        // instruction lines before this one = its rank in the warp's sorted line list
-        uint32_t lo = 0, hi = n_inst_w;
-        while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (wl_inst[mid] < o) lo = mid + 1; else hi = mid; }
-        const uint64_t first_inst = inst_base + lo;
+      const uint64_t inst_base = late ? 0 : exA[0] + P.off_inst, warp_base = late ? 0 : exA[2] + P.off_warp;
+      auto struct_line = [&](int o, uint32_t first_rel, uint32_t ex_tb, uint32_t ex_w) {
+        const unsigned c = text[o];
+        const uint64_t first_inst = inst_base + first_rel;
         SlParsed sp = parse_struct_line(text, text32, o);
         int32_t n = 0;
         if (sp.type == SL_WARP) {                     // trace_parser.cc:428-437: the next non-blank line must be "insts = n"
@@ -503,6 +513,27 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         }
         if (line_end(nlmap32, (unsigned)o) - (unsigned)o > (unsigned)TI_MAX_LINE) fl |= TI_EF_LINE_TOO_LONG;
         note_error(ms, fl, tbase + (uint32_t)o);
+      };
+      if (sl_listed) {
+        for (uint32_t e = tid; e < n_sl; e += kThreads) {
+          const uint4 ent = reinterpret_cast<const uint4 *>(smem + oSlList)[e];
+          struct_line((int)ent.x, ent.y, ent.z, ent.w);
+        }
+      } else {
+        uint32_t tb_seen = tb0, warp_seen = warp0;
+        for (uint32_t i0 = 0; i0 < n_sl_w; i0 += 32) {
+          const uint32_t i = i0 + lane;
+          const bool valid = i < n_sl_w;
+          const int o = valid ? wl_sl[i] : 0;
+          const unsigned c = valid ? text[o] : 0u;
+          const uint32_t tbb = __ballot_sync(kFull, c == 't'), wb = __ballot_sync(kFull, c == 'w');
+          const uint32_t ex_tb = tb_seen + __popc(tbb & lt), ex_w = warp_seen + __popc(wb & lt);
+          tb_seen += __popc(tbb); warp_seen += __popc(wb);
+          if (!valid) continue;
+          uint32_t lo = 0, hi = n_inst_w;            // instruction lines before this one = its rank in the warp's sorted line list
+          while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (wl_inst[mid] < o) lo = mid + 1; else hi = mid; }
+          struct_line(o, inst0 + lo, ex_tb, ex_w);
+        }
       }
     }
     TI_STAMP(6);   // H

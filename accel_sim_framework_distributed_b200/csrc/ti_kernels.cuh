@@ -71,7 +71,9 @@ constexpr int oTxnLoc = oTxnSlot + 2 * align16(kItems * 2);  // u16[2][kItems] e
 constexpr int oTxnCnt = oTxnLoc + 2 * align16(kItems * 2);   // u8 [2][kItems]
 constexpr int oMIo = oTxnCnt + 2 * align16(kItems);          // u8 [2][kItems] index of the instruction among the warp's records
 constexpr int oSlowQ = oMIo + 2 * align16(kItems);           // u16[kItems]    items waiting for the warp path
-constexpr int oCnt = oSlowQ + align16(kItems * 2);           // u32[kSmCnt]    counter mirror
+constexpr int kSlList = 128;                                 // structural lines of a chunk the CTA-wide pass takes (more: per warp)
+constexpr int oSlList = oSlowQ + align16(kItems * 2);        // uint4[kSlList] offset | instruction lines before | thread-block ordinal | warp ordinal
+constexpr int oCnt = oSlList + kSlList * 16;                 // u32[kSmCnt]    counter mirror
 constexpr int kWarpScratch = 32 * 6 * 4;                     // per warp: token offsets (decode), then B-group merge slots (coalesce)
 constexpr int oTok = oCnt + align16(kSmCnt * 4);
 constexpr int oNlMap = oTok + kWarps * kWarpScratch;      // u16[kTextBytes/16] newline bitmap of the staged text
