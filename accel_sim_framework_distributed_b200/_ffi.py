@@ -117,7 +117,7 @@ SYMBOLS = [
     "ti_plan_shards", "ti_parse_commandlist", "ti_parse_memcpy", "ti_decode_noalloc", "ti_kernel_decode_streamed",
     "ti_regroup_device", "ti_regroup_buffer", "ti_regroup_commandlist", "ti_regroup_buckets", "ti_kernel_coalesce_local", "ti_counters_derive", "ti_kernel_path_stats",
     "ti_kernel_decode_streamed_compact", "ti_expand_row", "ti_expand_txns",
-    "ti_compress_rows", "ti_kernel_pipeline_stats", "ti_kernel_decode_window_compact", "ti_kernel_host_body", "ti_nccl_unique_id", "ti_nccl_comm_create", "ti_nccl_comm_destroy", "ti_allreduce_counters",
+    "ti_compress_rows", "ti_kernel_pipeline_stats", "ti_kernel_decode_window_compact", "ti_kernel_host_body", "ti_kernel_release_text", "ti_nccl_unique_id", "ti_nccl_comm_create", "ti_nccl_comm_destroy", "ti_allreduce_counters",
 ]
 
 
@@ -172,6 +172,7 @@ def load_library(path=None):
         "ti_kernel_decode_streamed_compact": (C.c_int, [V, S, P(ViewCompact)]),
         "ti_kernel_decode_window_compact": (C.c_int, [V, S, S, S, P(ViewCompact)]),
         "ti_kernel_host_body": (C.c_int, [V, P(V), P(S)]),
+        "ti_kernel_release_text": (C.c_int, [V, S, S]),
         "ti_compress_rows": (C.c_int, [V, V, V, S, C.c_int, V, S, V, P(S)]),
         "ti_kernel_pipeline_stats": (C.c_int, [V, C.c_int, C.c_int, P(PipelineStats)]),
         "ti_expand_row": (None, [P(ViewCompact), U64, V]),

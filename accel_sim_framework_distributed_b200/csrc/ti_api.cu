@@ -886,6 +886,18 @@ extern "C" ti_status ti_kernel_host_body(ti_kernel *k, const char **body, size_t
   return TI_OK;
 }
 
+extern "C" ti_status ti_kernel_release_text(ti_kernel *k, size_t begin, size_t end) {
+  if (!k || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
+#ifndef TI_EMU
+  if (k->map_base && end > begin) {   // whole pages inside the range: the page cache keeps them, this process lets go of them
+    const size_t page = (size_t)sysconf(_SC_PAGESIZE);
+    const uintptr_t lo = ((uintptr_t)(k->h_body + begin) + page - 1) & ~(uintptr_t)(page - 1), hi = (uintptr_t)(k->h_body + end) & ~(uintptr_t)(page - 1);
+    if (hi > lo) madvise((void *)lo, hi - lo, MADV_DONTNEED);
+  }
+#endif
+  return TI_OK;
+}
+
 extern "C" ti_status ti_kernel_decode_window_compact(ti_kernel *k, size_t begin, size_t end, size_t shard_bytes, ti_view_compact *vc) {
   if (!k || !vc || begin > end || end > k->body_len) return TI_ERR_INVALID_ARG;
   if (!k->h_body && k->body_len) { ti::set_error("ti_kernel_decode_window_compact needs a host-resident body"); return TI_ERR_STATE; }

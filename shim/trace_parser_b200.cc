@@ -277,6 +277,7 @@ void trace_parser::get_next_threadblock_traces(std::vector<std::vector<inst_trac
     memset(&s.view, 0, sizeof s.view);
   }
   while (s.next_tb >= s.view.counts.n_tb) {   // the window is used up (or none decoded yet): next non-empty one
+    if (s.next_window > 0) ti_kernel_release_text(s.k, s.cuts[s.next_window - 1], s.cuts[s.next_window]);   // the window just used up
     if (s.next_window + 1 >= s.cuts.size()) return;  // the reference's loop ends at EOF with nothing filled
     const size_t b = s.cuts[s.next_window], e = s.cuts[s.next_window + 1];
     ++s.next_window;
