@@ -100,7 +100,8 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
   // what the warp path staged.  The records left earlier with a scratch value in mem_idx; the row index
   // is patched here.  After the look-back every warp handles the items of its own range.
   // `recompute` (CTA-uniform): the staging area overflowed, so the spilled warp-path instructions are
-  // coalesced again from their address rows, which needs the chunk's records: same iteration only.
+  // coalesced again from their address rows and their records, both read back from global memory (the
+  // warp that reads a record is the one whose bulk store wrote it).
   auto finish = [&](uint32_t c, unsigned par, uint32_t n_mem, uint32_t n_txn_chunk, uint64_t base_inst,
                     bool have_mem, uint64_t base_mem, bool recompute, const LbPre *pre) {
     if (lane == 0) bulk_store_wait_all();              // this warp's record block is in global memory: the patch below lands on top of it
@@ -193,7 +194,15 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
       for (uint32_t j = 0; j < pw.n_mem; ++j) {
         if (txn_slot[j] != 0xFFFFu || !txn_cnt[j]) continue;
         const uint64_t at = wtxn + txn_loc[j];
-        const ti_inst_rec *rp = recs + wid * kWarpInst + m_io[j];
+        const uint64_t ri = winst + m_io[j];
+        if (ri >= P.cap_inst) continue;                // the record table overflowed: the host decodes again
+        ti_inst_rec rr;
+        {
+          const uint4 *g = reinterpret_cast<const uint4 *>(P.inst + ri);
+          uint4 *d = reinterpret_cast<uint4 *>(&rr);
+          d[0] = __ldcg(g); d[1] = __ldcg(g + 1);
+        }
+        const ti_inst_rec *rp = &rr;
         const uint64_t row = wmem + j;
         const uint64_t addr = row < P.cap_mem ? __ldcg(P.rows + row * 32 + lane) : 0;   // written by the warp path
         const unsigned ds = rp->data_size, pack_b = rp->pack_b, op = rp->op;
@@ -212,7 +221,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     }
     __syncthreads();   // the pool may be reused
   };
-  bool pend = false, pend_have_mem = false;   // a chunk whose rows and transactions are still parked in shared memory (CTA-uniform)
+  bool pend = false, pend_have_mem = false, pend_recompute = false;   // a chunk whose rows and transactions are still parked in shared memory (CTA-uniform)
   uint32_t pend_chunk = 0, pend_n_mem = 0, pend_n_txn = 0;
   unsigned pend_par = 0;
   uint64_t pend_base_inst = 0, pend_base_mem = 0;
@@ -426,7 +435,10 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     const uint32_t n_warp_path = ms->n_slowq;               // CTA-uniform
     if (lane == 0) { WarpPre q; q.inst0 = (uint16_t)inst0; q.mem0 = (uint16_t)mem0; q.n_mem = (uint16_t)mem_seen; q.n_notes = (uint16_t)n_notes_w; q.txn0 = txn0; ms->pw[par][wid] = q; }
     const unsigned long long aggA0 = chain_pack(n_inst, n_tb), aggA1 = chain_pack(n_warp, 0);
-    if (tid == 0) { chain_publish(P.chain[0], chunk, aggA0); chain_publish(P.chain[1], chunk, aggA1); chain_publish(P.chain[2], chunk, chain_pack(n_mem, 0)); }
+    if (tid == 0) {
+      chain_publish(P.chain[0], chunk, aggA0); chain_publish(P.chain[1], chunk, aggA1); chain_publish(P.chain[2], chunk, chain_pack(n_mem, 0));
+      if (!n_warp_path) chain_publish(P.chain[3], chunk, chain_pack(n_txn_chunk, 0));   // every transaction count is known already
+    }
 
     // the warps list their structural lines for the CTA-wide pass H (if the chunk's lines fit the list)
     const bool sl_listed = n_sl <= (uint32_t)kSlList;          // CTA-uniform
@@ -451,7 +463,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     // (before anything of this chunk goes into the pool)
     if (pend) {
       const LbPre preF = pend_have_mem ? cta_lookahead(P.chain[3], nullptr, pend_chunk) : cta_lookahead(P.chain[2], P.chain[3], pend_chunk);
-      finish(pend_chunk, pend_par, pend_n_mem, pend_n_txn, pend_base_inst, pend_have_mem, pend_base_mem, false, &preF);
+      finish(pend_chunk, pend_par, pend_n_mem, pend_n_txn, pend_base_inst, pend_have_mem, pend_base_mem, pend_recompute, &preF);
       pend = false;
     } else __syncthreads();                                // Misc::pw visible to the warp path below
     TI_STAMP(5);   // S + F'
@@ -634,7 +646,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     TI_STAMP(7);   // M
 
     // ---------------------------------------------------------------- T chain 3; next ticket; chains 0 / 1 resolve
-    if (tid == 0) chain_publish(P.chain[3], chunk, chain_pack(n_txn_chunk, 0));
+    if (tid == 0 && n_warp_path) chain_publish(P.chain[3], chunk, chain_pack(n_txn_chunk, 0));
     if (tid == kThreads - 32) ms->chunk_next = atomicAdd(&P.g->ticket, 1u);   // visible after the barriers of the resolve below
     if (late) {
       const LbPre preA = cta_lookahead(P.chain[0], P.chain[1], chunk);
@@ -699,20 +711,15 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
     if (chunk_next < P.n_chunks) fill_edges(chunk_next, nbuf);
     TI_STAMP(9);   // headers, records out
 
-    // ---------------------------------------------------------------- F: now, or parked for the next iteration
-    // Not parked when staging overflowed: the recompute needs this chunk's records, which the next chunk overwrites.
-    if (stage_used > stage_cap) {
-      if (tid == 0) atomicAdd(&P.g->rare[0], 1u);
-      __syncthreads();
-      finish(chunk, par, n_mem, n_txn_chunk, base_inst, n_warp_path != 0, base_mem, true, nullptr);
-    } else {
-      pend = true; pend_chunk = chunk; pend_par = par; pend_n_mem = n_mem; pend_n_txn = n_txn_chunk;
-      pend_base_inst = base_inst; pend_have_mem = n_warp_path != 0; pend_base_mem = base_mem;
-    }
-    TI_STAMP(10);  // F (staging overflow only)
+    // ---------------------------------------------------------------- F: parked for the next iteration
+    // (a chunk whose transactions overflowed the staging area included: what was spilled is coalesced again there)
+    if (stage_used > stage_cap && tid == 0) atomicAdd(&P.g->rare[0], 1u);
+    pend = true; pend_chunk = chunk; pend_par = par; pend_n_mem = n_mem; pend_n_txn = n_txn_chunk;
+    pend_base_inst = base_inst; pend_have_mem = n_warp_path != 0; pend_base_mem = base_mem; pend_recompute = stage_used > stage_cap;
+    TI_STAMP(10);
     if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }
   }
-  if (pend) finish(pend_chunk, pend_par, pend_n_mem, pend_n_txn, pend_base_inst, pend_have_mem, pend_base_mem, false, nullptr);
+  if (pend) finish(pend_chunk, pend_par, pend_n_mem, pend_n_txn, pend_base_inst, pend_have_mem, pend_base_mem, pend_recompute, nullptr);
   if (lane == 0) bulk_store_wait_all();
 #pragma unroll
   for (int d = 16; d; d >>= 1) fast_lines += __shfl_xor_sync(kFull, fast_lines, d);
