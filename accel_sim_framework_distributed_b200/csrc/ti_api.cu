@@ -77,6 +77,19 @@ void set_chains(ti::DecodeParams &P, void *base, uint32_t n_chunks) {
   for (int i = 0; i < ti::kChains; ++i) P.chain[i] = (unsigned long long *)base + (size_t)i * (n_chunks + 1);
 }
 
+// zero what a launch of the fused kernel starts from (ti_reset_kernel)
+ti_status reset_launch_state(cudaStream_t s, void *chains, uint32_t n_chunks, void *globals, void *counters, void *txn_off) {
+  const uint64_t n_words = ti::chain_bytes(n_chunks) / 8;
+  const int grid = (int)std::min<uint64_t>(64, (n_words + 255) / 256 + 1);
+#ifdef TI_EMU
+  emu::launch(dim3(grid), dim3(256), 0, [=]() { ti::ti_reset_kernel((unsigned long long *)chains, n_words, (ti::Globals *)globals, (unsigned long long *)counters, (uint32_t *)txn_off); });
+#else
+  ti::ti_reset_kernel<<<grid, 256, 0, s>>>((unsigned long long *)chains, n_words, (ti::Globals *)globals, (unsigned long long *)counters, (uint32_t *)txn_off);
+#endif
+  CK(cudaGetLastError());
+  return TI_OK;
+}
+
 int arch_column(unsigned v) {  // trace_driven.cc:100-118
   switch (v) {
     case 35: return 0;
@@ -524,11 +537,7 @@ static ti_status launch_decode(ti_kernel *k) {
   P.shmem_limited_broadcast = cfg.shmem_limited_broadcast; P.gmem_skip_L1D = cfg.gmem_skip_L1D;
 
   CK(cudaEventRecord(c->ev0, s));
-  CK(cudaMemsetAsync(k->chains.p, 0, ti::chain_bytes(n_chunks), s));
-  CK(cudaMemsetAsync(k->globals.p, 0, sizeof(ti::Globals), s));
-  CK(cudaMemsetAsync(&((ti::Globals *)k->globals.p)->first_error_off, 0xff, 4, s));   // atomicMin target
-  CK(cudaMemsetAsync(k->counters.p, 0, sizeof(ti_counters), s));
-  CK(cudaMemsetAsync(k->txn_off.p, 0, 4, s));
+  { const ti_status rs = reset_launch_state(s, k->chains.p, n_chunks, k->globals.p, k->counters.p, k->txn_off.p); if (rs != TI_OK) return rs; }
   if (n_chunks) {
     const int grid = (int)std::min<uint32_t>((uint32_t)c->grid, n_chunks);
 #ifdef TI_EMU
@@ -680,12 +689,23 @@ static ti_status decode_streamed_impl(ti_kernel *k, size_t shard_bytes, ti_view 
   }
 
   cudaStream_t s_c = c->stream, s_up = ss->s_h2d, s_dn = ss->s_d2h;
+#ifdef TI_STREAM_TRACE   // tuning builds: a timeline of the three streams, printed at the end (tools/e2e_diag.py)
+  std::vector<cudaEvent_t> tr(6 * (size_t)n_sh + 1);
+  for (cudaEvent_t &e : tr) cudaEventCreate(&e);
+  cudaEventRecord(tr[6 * (size_t)n_sh], s_c);
+  cudaStreamWaitEvent(s_up, tr[6 * (size_t)n_sh], 0);
+#define TI_TR(i, j, s) cudaEventRecord(tr[6 * (size_t)(i) + (j)], s)
+#else
+#define TI_TR(i, j, s) do { } while (0)
+#endif
   auto h2d = [&](int i) -> ti_status {   // text of shard i -> its buffer set
     StreamSet &t = ss->set[i & 1];
     const size_t n = cuts[i + 1] - cuts[i];
     if (i >= 2) CK(cudaStreamWaitEvent(s_up, t.ev_dec, 0));   // decode(i-2) has finished reading this buffer
+    TI_TR(i, 0, s_up);
     if (n) CK(cudaMemcpyAsync(t.text.p, k->h_body + cuts[i], n, cudaMemcpyHostToDevice, s_up));
     CK(cudaEventRecord(t.ev_h2d, s_up));
+    TI_TR(i, 1, s_up);
     return TI_OK;
   };
 
@@ -719,11 +739,7 @@ static ti_status decode_streamed_impl(ti_kernel *k, size_t shard_bytes, ti_view 
     CK(cudaStreamWaitEvent(s_c, t.ev_h2d, 0));
     if (i >= 2) CK(cudaStreamWaitEvent(s_c, t.ev_d2h, 0));    // D2H(i-2) has drained this set's outputs
     CK(cudaEventRecord(t.t0, s_c));
-    CK(cudaMemsetAsync(t.chains.p, 0, ti::chain_bytes(n_chunks), s_c));
-    CK(cudaMemsetAsync(t.globals.p, 0, sizeof(ti::Globals), s_c));
-    CK(cudaMemsetAsync(&((ti::Globals *)t.globals.p)->first_error_off, 0xff, 4, s_c));
-    CK(cudaMemsetAsync(t.counters.p, 0, sizeof(ti_counters), s_c));
-    CK(cudaMemsetAsync(t.txn_off.p, 0, 4, s_c));
+    if ((st = reset_launch_state(s_c, t.chains.p, n_chunks, t.globals.p, t.counters.p, t.txn_off.p)) != TI_OK) return st;
     if (n_chunks) {
       const int grid = (int)std::min<uint32_t>((uint32_t)c->grid, n_chunks);
 #ifdef TI_EMU
@@ -758,14 +774,24 @@ static ti_status decode_streamed_impl(ti_kernel *k, size_t shard_bytes, ti_view 
       CK(cudaGetLastError());
     }
     CK(cudaEventRecord(t.t1, s_c));
+    TI_TR(i, 2, s_c);
     ti::Globals *g = (ti::Globals *)t.small.p;
     ti_counters *hc = (ti_counters *)((char *)t.small.p + sizeof(ti::Globals));
     uint32_t *hkeep = (uint32_t *)((char *)t.small.p + sizeof(ti::Globals) + sizeof(ti_counters));   // rows / transactions the compact pass kept
-    hkeep[0] = hkeep[1] = 0;
-    CK(cudaMemcpyAsync(g, t.globals.p, sizeof(ti::Globals), cudaMemcpyDeviceToHost, s_c));
-    CK(cudaMemcpyAsync(hc, t.counters.p, sizeof(ti_counters), cudaMemcpyDeviceToHost, s_c));
-    if (cp_blocks) CK(cudaMemcpyAsync(hkeep, (uint32_t *)t.part.p + 2 * (size_t)cp_blocks, 8, cudaMemcpyDeviceToHost, s_c));
+    {
+      const ti::Globals *dg = (const ti::Globals *)t.globals.p;
+      const unsigned long long *dc = (const unsigned long long *)t.counters.p;
+      const uint32_t *dk = cp_blocks ? (const uint32_t *)t.part.p + 2 * (size_t)cp_blocks : nullptr;
+      unsigned char *hp = (unsigned char *)t.small.p;
+#ifdef TI_EMU
+      emu::launch(dim3(1), dim3(256), 0, [=]() { ti::ti_publish_kernel(dg, dc, dk, hp); });
+#else
+      ti::ti_publish_kernel<<<1, 256, 0, s_c>>>(dg, dc, dk, hp);   // pinned host memory is device-addressable under unified addressing
+#endif
+      CK(cudaGetLastError());
+    }
     CK(cudaEventRecord(t.ev_dec, s_c));
+    TI_TR(i, 3, s_c);
     if (i + 2 < n_sh && (st = h2d(i + 2)) != TI_OK) return st;  // queued behind ev_dec of this set
     CK(cudaEventSynchronize(t.ev_dec));                         // the shard's counts are on the host now
     float ms = 0;
@@ -795,6 +821,7 @@ static ti_status decode_streamed_impl(ti_kernel *k, size_t shard_bytes, ti_view 
     }
     // results of shard i -> host, behind its decode
     CK(cudaStreamWaitEvent(s_dn, t.ev_dec, 0));
+    TI_TR(i, 4, s_dn);
     auto down = [&](HostBuf &h, uint64_t at, const DevBuf &d, uint64_t n, size_t elt) -> ti_status {
       if (n) CK(cudaMemcpyAsync((char *)h.p + at * elt, d.p, n * elt, cudaMemcpyDeviceToHost, s_dn));
       return TI_OK;
@@ -807,6 +834,7 @@ static ti_status decode_streamed_impl(ti_kernel *k, size_t shard_bytes, ti_view 
     if ((st = down(k->h_tb, T_tb, t.tb, hc->n_tb, sizeof(ti_tb_rec))) != TI_OK) return st;
     if ((st = down(k->h_warp, T_warp, t.warp, hc->n_warp, sizeof(ti_warp_rec))) != TI_OK) return st;
     CK(cudaEventRecord(t.ev_d2h, s_dn));
+    TI_TR(i, 5, s_dn);
     T_inst += hc->n_inst; T_mem += hc->n_mem; T_txn += hc->n_txn; T_tb += hc->n_tb; T_warp += hc->n_warp;
     T_full += hkeep[0]; T_keep += hkeep[1];
     ti_counters_add(&total, hc);
@@ -814,6 +842,17 @@ static ti_status decode_streamed_impl(ti_kernel *k, size_t shard_bytes, ti_view 
   CK(cudaStreamSynchronize(s_dn));
   CK(cudaStreamSynchronize(s_up));
   CK(cudaStreamSynchronize(s_c));
+#ifdef TI_STREAM_TRACE
+  if (getenv("TI_STREAM_TRACE")) {
+    fprintf(stderr, "shard: upload [start end]  decode kernels end / counts on host  download [start end]  (ms)\n");
+    for (int i = 0; i < n_sh; ++i) {
+      float v[6];
+      for (int j = 0; j < 6; ++j) cudaEventElapsedTime(&v[j], tr[6 * (size_t)n_sh], tr[6 * (size_t)i + j]);
+      fprintf(stderr, "%3d: up %6.2f %6.2f  dec(end) %6.2f  counts %6.2f  down %6.2f %6.2f\n", i, v[0], v[1], v[2], v[3], v[4], v[5]);
+    }
+  }
+  for (cudaEvent_t &e : tr) cudaEventDestroy(e);
+#endif
   if (overflow) {
     // a capacity guess was too small for one shard: take the one-piece path, which re-decodes with exact sizes
     if ((st = ti_kernel_upload(k, 0, k->body_len)) != TI_OK) return st;
@@ -1000,11 +1039,7 @@ extern "C" ti_status ti_decode_noalloc(ti_ctx *c, const ti_noalloc_io *io, void 
   P.shmem_limited_broadcast = cfg.shmem_limited_broadcast; P.gmem_skip_L1D = cfg.gmem_skip_L1D;
 
   // what must start at zero: the table entries this call uses, the status block, the counters
-  CK(cudaMemsetAsync(scratch, 0, ti::chain_bytes(n_chunks), s));
-  CK(cudaMemsetAsync(io->d_status, 0, sizeof(ti::Globals), s));
-  CK(cudaMemsetAsync(&((ti::Globals *)io->d_status)->first_error_off, 0xff, 4, s));
-  CK(cudaMemsetAsync(io->d_counters, 0, sizeof(ti_counters), s));
-  CK(cudaMemsetAsync(io->d_txn_off, 0, 4, s));
+  { const ti_status rs = reset_launch_state(s, scratch, n_chunks, io->d_status, io->d_counters, io->d_txn_off); if (rs != TI_OK) return rs; }
   if (n_chunks) {
     const int grid = (int)std::min<uint32_t>((uint32_t)c->grid, n_chunks);
 #ifdef TI_EMU

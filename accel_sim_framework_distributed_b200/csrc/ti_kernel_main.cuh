@@ -748,5 +748,34 @@ __global__ void ti_check_kernel(const ti_warp_rec *warp, uint64_t cap_warp, cons
   }
 }
 
+// What a launch needs at zero: the look-back words it will use, the status block (first_error_off: all ones, it
+// is an atomicMin target), the counter block and the CSR sentinel.  One kernel instead of five memsets: a memset
+// may be queued on a copy engine behind a large transfer of another stream, which stalls the decode behind it.
+__global__ void ti_reset_kernel(unsigned long long *chains, uint64_t n_words, Globals *g, unsigned long long *counters, uint32_t *txn_off) {
+  const uint64_t t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = t0; i < n_words; i += stride) chains[i] = 0;
+  for (uint64_t i = t0; i < sizeof(ti_counters) / 8; i += stride) counters[i] = 0;
+  if (t0 == 0) {
+    Globals z;
+    z.ticket = z.error_flags = z.overflow = 0; z.first_error_off = 0xffffffffu;
+    z.rare[0] = z.rare[1] = z.rare[2] = z.rare[3] = 0;
+    *g = z;
+    txn_off[0] = 0;
+  }
+}
+
+// A shard's status, counters and (compact results) kept-row / kept-transaction totals, written by the GPU straight
+// into pinned host memory: no copy engine involved, so they are not queued behind the previous shard's results.
+__global__ void ti_publish_kernel(const Globals *g, const unsigned long long *counters, const uint32_t *keep, unsigned char *host) {
+  static_assert(sizeof(Globals) % 8 == 0 && sizeof(ti_counters) % 8 == 0, "publish layout");
+  const unsigned t = threadIdx.x;                    // one CTA
+  if (t < sizeof(Globals) / 4) reinterpret_cast<uint32_t *>(host)[t] = reinterpret_cast<const uint32_t *>(g)[t];
+  for (unsigned i = t; i < sizeof(ti_counters) / 8; i += blockDim.x) reinterpret_cast<unsigned long long *>(host + sizeof(Globals))[i] = counters[i];
+  if (t < 2) reinterpret_cast<uint32_t *>(host + sizeof(Globals) + sizeof(ti_counters))[t] = keep ? keep[t] : 0u;
+#ifndef TI_EMU
+  __threadfence_system();
+#endif
+}
+
 }  // namespace ti
 #endif
