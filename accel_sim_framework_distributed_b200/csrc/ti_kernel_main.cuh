@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         P.counters[kCntNInst + 2] = base_txn + n_txn_chunk;
       }
     }
+    TI_STAMP(11);  // (S +) F: look-back
     const WarpPre pw = ms->pw[par][wid];
     const StrideNote *wnotes = reinterpret_cast<const StrideNote *>(smem + oNotes) + (par * kWarps + wid) * kNotesPerWarp;
     const StrideNote *cnotes = reinterpret_cast<const StrideNote *>(smem + oNotes) + par * kWarps * kNotesPerWarp;
@@ -158,6 +159,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         }
       }
     }
+    TI_STAMP(12);  // F: rows
     // per memory instruction: CSR offset and the row index in its record
     for (uint32_t j = lane; j < pw.n_mem; j += 32) {
       const uint64_t row = wmem + j;
@@ -190,6 +192,7 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         for (uint32_t k = sub; k < room; k += 4) { dst[2 * k] = src[2 * k]; dst[2 * k + 1] = src[2 * k + 1]; }
       }
     }
+    TI_STAMP(13);  // F: offsets, record patch, transactions
     if (recompute) {                                   // CTA-uniform
       for (uint32_t j = 0; j < pw.n_mem; ++j) {
         if (txn_slot[j] != 0xFFFFu || !txn_cnt[j]) continue;

@@ -29,8 +29,8 @@ tp.lib.ti_debug_phase_cycles(out)
 k.decode(); k.sync()
 ms = k.decode_ms()
 tp.lib.ti_debug_phase_cycles(out)
-names = ["top of loop", "P0 wait text", "P1 classify", "W line starts", "W tokenize + stride + counters", "S prefixes + F' previous chunk out",
-         "H structural lines", "M warp path", "T resolve chains 0/1", "headers + records out", "F own chunk (staging overflow)", "-", "-", "-", "-"]
+names = ["top of loop", "P0 wait text", "P1 classify", "W line starts", "W tokenize + stride + counters", "F tail (recompute, barrier)",
+         "H structural lines", "M warp path", "T resolve chains 0/1", "headers + records out", "loop tail", "(in S + F') S + look-back of F", "(in S + F') F rows", "(in S + F') F offsets, patch, transactions", "-"]
 tot = sum(out[:15])
 print("decode %.3f ms; thread-0 cycles per phase (share of the CTA's time):" % ms)
 for n, v in zip(names, out):
