@@ -283,11 +283,18 @@ def shim_block(img, window_mb=256):
         open(os.path.join(tmp, "kernelslist.g"), "w").write("kernel-1.traceg\n")
         for name, exe in (("drop_in_b200", shim), ("reference", ref)):
             r = subprocess.run([exe, "time", "./kernelslist.g"], cwd=tmp, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True,
-                               env=dict(os.environ, TI_SHIM_WINDOW_MB=str(window_mb)))
+                               env=dict(os.environ, TI_SHIM_WINDOW_MB=str(window_mb), TI_SHIM_TIMING="1"))
             try:
-                d = json.loads(r.stderr.strip().splitlines()[-1])
+                lines = r.stderr.strip().splitlines()
+                d = json.loads([l for l in lines if l.startswith("{")][-1])
                 d["warp_insts_per_s"] = d["n_inst"] / d["seconds"]
                 d["GB_per_s"] = len(img) / d["seconds"] / 1e9
+                for l in lines:   # the drop-in's own split of its wall time (TI_SHIM_TIMING)
+                    if l.startswith("trace_parser(b200): ti_ctx_create"):
+                        w = l.replace(",", " ").split()
+                        d["ctx_create_s"], d["window_decode_s"] = float(w[2]), float(w[6])
+                        d["hand_out_s"] = round(d["seconds"] - d["ctx_create_s"] - d["window_decode_s"], 3)
+                        d["note"] = "ctx_create_s = CUDA context + module load, once per process; window_decode_s = uploads, fused kernel, gather, downloads"
                 out[name] = d
             except Exception:
                 out[name] = {"failed": r.returncode, "stderr": r.stderr[-300:]}

@@ -49,6 +49,25 @@ struct KernelState {
   uint64_t next_tb = 0;                // next thread block of the current window
 };
 
+// get_datawidth_from_opcode(get_opcode_tokens()) without building the token vector: the first '.'-separated token that
+// is all digits, or 'U' followed by digits, gives the width in bits (trace_parser.cc:16-20,51-76); 4 bytes otherwise
+unsigned width_from_opcode(const char *p, size_t n) {
+  size_t b = 0;
+  while (b < n) {
+    size_t e = b;
+    while (e < n && p[e] != '.') ++e;
+    const size_t d = b + (p[b] == 'U' ? 1 : 0);
+    if (d < e) {
+      unsigned long v = 0;
+      size_t i = d;
+      for (; i < e && p[i] >= '0' && p[i] <= '9'; ++i) v = v * 10 + (unsigned long)(p[i] - '0');
+      if (i == e) return (unsigned)v / 8;
+    }
+    b = e + 1;
+  }
+  return 4;
+}
+
 size_t window_bytes() {
   if (const char *b = getenv("TI_SHIM_WINDOW_BYTES")) { const long long v = atoll(b); if (v > 0) return (size_t)v; }   // (tests: tiny windows)
   const char *e = getenv("TI_SHIM_WINDOW_MB");
@@ -65,10 +84,13 @@ extern "C" void trace_parser_b200_set_config(const ti_config *cfg) { g_cfg = *cf
 struct trace_parser::impl {
   ti_ctx *ctx = nullptr;
   std::unordered_map<std::ifstream *, KernelState> kernels;
+  double s_ctx = 0, s_decode = 0;      // TI_SHIM_TIMING=1: seconds in ti_ctx_create / in the window decodes, printed by the destructor
   ti_ctx *context() {
     if (!ctx) {
       if (!g_cfg_set) ti_config_qv100(&g_cfg);
+      const auto t0 = std::chrono::steady_clock::now();
       ti_status st = ti_ctx_create(&g_cfg, &ctx);
+      s_ctx += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
       if (st != TI_OK) die("ti_ctx_create", st);
     }
     return ctx;
@@ -175,6 +197,7 @@ bool inst_trace_t::parse_from_string(std::string trace, unsigned trace_version) 
 trace_parser::trace_parser(const char *kernellist_filepath) : m(new impl) { kernellist_filename = kernellist_filepath; }
 
 trace_parser::~trace_parser() {
+  if (getenv("TI_SHIM_TIMING")) fprintf(stderr, "trace_parser(b200): ti_ctx_create %.3f s, window decodes %.3f s\n", m->s_ctx, m->s_decode);
   for (auto &kv : m->kernels) ti_kernel_close(kv.second.k);
   if (m->ctx) ti_ctx_destroy(m->ctx);
   delete m;
@@ -282,7 +305,9 @@ void trace_parser::get_next_threadblock_traces(std::vector<std::vector<inst_trac
     const size_t b = s.cuts[s.next_window], e = s.cuts[s.next_window + 1];
     ++s.next_window;
     if (e == b) continue;
+    const auto t0 = std::chrono::steady_clock::now();
     ti_status st = ti_kernel_decode_window_compact(s.k, b, e, 0, &s.view);  // copies and kernel overlapped inside
+    m->s_decode += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (st != TI_OK) die("get_next_threadblock_traces", st);
     s.next_tb = 0;
   }
@@ -310,7 +335,7 @@ void trace_parser::get_next_threadblock_traces(std::vector<std::vector<inst_trac
         t.memadd_info = new inst_memadd_info_t();
         ti_expand_row(&v, r.mem_idx, (uint64_t *)t.memadd_info->addrs);   // 16 B descriptor -> inst_memadd_info_t::addrs
         // inst_trace_t keeps the opcode-derived width (the LDC override belongs to the next stage)
-        t.memadd_info->width = (int32_t)t.get_datawidth_from_opcode(t.get_opcode_tokens());
+        t.memadd_info->width = (int32_t)width_from_opcode(v.text + r.opc_off, r.opcode_len);
       }
     }
   }
