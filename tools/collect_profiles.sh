@@ -11,5 +11,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 # one steady-state launch of the dominant kernel, full set
 ncu --set full --clock-control none --import-source on -k regex:ti_decode_kernel -s 4 -c 1 -o $o/full -f python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-extras > $o/full_run.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:ti_decode_kernel -s 4 -c 1 -o $o/full_config3 -f python bench.py --workload config3 --steps 3 --warmup 3 --no-cpu-baseline --no-e2e --no-extras > $o/full_config3_run.log 2>&1
-TI_LIB=$PWD/build/phase/libti_phase.so python tools/phase_timing.py config2 > $o/phase_config2.txt 2>&1
+TI_LIB=$PWD/build/phase.so python tools/phase_timing.py config2 > $o/phase_config2.txt 2>&1
+TI_LIB=$PWD/build/phase.so python tools/phase_timing.py config3 > $o/phase_config3.txt 2>&1
+python tools/e2e_diag.py > $o/e2e_diag.txt 2>&1
 ls -la $o
