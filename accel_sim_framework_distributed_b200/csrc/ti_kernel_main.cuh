@@ -363,7 +363,17 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         const unsigned ds = rhi.z >> 16 & 0xff, op = rhi.y >> 16 & 0xff;
         StrideDesc d;
         uint32_t fl = 0;
-        if (fo >= (unsigned)kNotesPerWarp || !stride_parse_fast(text, dlmap32, tmp & 0xffff, le, mask, ds ? ds : 1, d, fl)) {
+        bool parsed;
+        if ((tmp >> 16 & 3) == 2) {
+          // one active lane in base+delta form: "0x<base> <immediate>".  Whatever the fast token reader does not take
+          // (no immediate, a long one, ...) is left to the warp path, which reads it the way the reference's stream does.
+          uint64_t b;
+          int64_t imm;
+          parsed = stride_tokens_fast(text, text32, dlmap32, tmp & 0xffff, le, b, imm);
+          d.base = b; d.stride = (int64_t)(ds ? ds : 1); d.first = 0; d.n = 0;   // a run of one: the stride is never applied
+          parsed = parsed && stride_finish(mask, ds ? ds : 1, d);
+        } else parsed = stride_parse_fast(text, dlmap32, tmp & 0xffff, le, mask, ds ? ds : 1, d, fl);
+        if (fo >= (unsigned)kNotesPerWarp || !parsed) {
           // no room for a descriptor, or the progression wraps around 2^64 (not monotone): warp path
           to_warp_path = true;
           if (fo < (unsigned)kNotesPerWarp) notes[fo].meta = 1u << 28; else atomicAdd(&P.g->rare[3], 1u);

@@ -323,8 +323,11 @@ TI_D uint32_t opcode_words(OpWords &o, uint64_t f, uint32_t mask, bool has_mem, 
   o.w6 = (nsrc | ndst << 3 | memory_op << 4 | atomic << 6 | cconst << 7) | (space | cache_op << 4 | (has_mem ? 1u : 0u) << 7) << 8 | (data_size & 0xff) << 16;
   o.w7 = (lat & 0xffff) | (init & 0xff) << 16 | (opcode_len & 0xff) << 24;
   o.w3 = has_mem ? memtmp_make(q, mode, resolve) : 0xFFFFFFFFu;
-  // base+stride global loads/stores take the thread-per-instruction path (ti_mem.cuh)
-  o.kind = has_mem ? ((mode == 1 && stridable) ? 3u : 1u) : 0u;
+  // base+stride global loads/stores take the thread-per-instruction path (ti_mem.cuh), and so does the form the tracer
+  // writes for ONE active lane: base+delta without deltas (its base+stride compressor needs a second lane,
+  // tracer_tool.cu:609-614), which is a run of one
+  const bool one_lane = mode == 2 && mask != 0 && (mask & (mask - 1)) == 0;
+  o.kind = has_mem ? (((mode == 1 || one_lane) && stridable) ? 3u : 1u) : 0u;
   return fl;
 }
 

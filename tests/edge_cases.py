@@ -125,8 +125,36 @@ W0 = [
     "0340 ffffffff 0 EXIT 0 0 0",
 ]
 
+# One active lane: the tracer's base+stride compressor gives up (no second lane to take a stride from,
+# tracer_tool.cu:609-614), so the line comes in base+delta form without deltas: base, then the immediate.
+W_SINGLE = [
+    "0000 00000001 1 R2 LDG.E.SYS 1 R4 4 2 0x7f0000004100 0",
+    "0010 80000000 0 STG.E.SYS 2 R4 R6 4 2 0x7f0000004104 0",
+    # straddles a 32 B sector / a 128 B line
+    "0020 00010000 1 R2 LDG.E.64.SYS 1 R4 8 2 0x7f000000411c 0",
+    "0030 00000100 1 R2 LDG.E.128.SYS 1 R4 16 2 0x7f0000004178 0",
+    # no immediate behind the base; a negative and a long one; upper-case 0X; address 0 (no access)
+    "0040 00000002 1 R2 LDG.E.SYS 1 R4 4 2 0x7f0000004200",
+    "0050 00000004 1 R2 LDG.E.SYS 1 R4 4 2 0x7f0000004204 -12",
+    "0060 00000008 1 R2 LDG.E.SYS 1 R4 4 2 0X7F0000004208 1234567890",
+    "0070 00000010 1 R2 LDG.E.SYS 1 R4 4 2 0x0 0",
+    # the same through a byte and a half-word width; an unaligned word
+    "0080 00000020 1 R2 LDG.E.U8.SYS 1 R4 1 2 0x7f0000004301 0",
+    "0090 00000040 0 STG.E.U16.SYS 2 R4 R6 2 2 0x7f0000004302 0",
+    "00a0 00000080 1 R2 LDG.E.SYS 1 R4 4 2 0x7f0000004306 0",
+    # not the global space / atomic / generic: these stay with the warp path
+    "00b0 00000001 1 R2 LDS.U.32 1 R4 4 2 0x100 0",
+    "00c0 00000001 1 R2 ATOMG.E.ADD.STRONG.GPU 2 R4 R6 4 2 0x7f0000004400 0",
+    "00d0 00000001 1 R2 LD.E.SYS 1 R4 4 2 0x7f0000004500 0",
+    # two active lanes in base+delta form next to them
+    "00e0 00000101 1 R2 LDG.E.SYS 1 R4 4 2 0x7f0000004600 256 0",
+    "00f0 ffffffff 0 EXIT 0 0 0",
+]
+
 VALID = {
     # name: (image bytes, config overrides)
+    "edge_single_lane": (image([(0, 0, 0, [W_SINGLE, W_SINGLE[:4]]), (1, 0, 0, [W_SINGLE[4:], []])]), {}),
+    "edge_single_lane_fermi": (image([(0, 0, 0, [W_SINGLE])]), dict(coalesce_arch=20)),
     "edge_v3": (image([(0, 0, 0, [W0, []]), (1, 0, 0, [W0[:5], W0[5:9]])]), {}),
     "edge_v2_prefix": (image([(0, 0, 0, [W0, []])], tv=2), {}),
     "edge_no_bases": (image([(0, 0, 0, [W0])], shmem=0, local=0), {}),
