@@ -186,10 +186,14 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
           if (!P.desc)
             for (unsigned k = sub; k < room; k += 4) txn_store(P.txn + at + k, dense_txn(d, ds, seg, is_write ? 4u : 0u, is_write, k));
         } else if (sub == 0) stride_emit(d, ds, seg, is_write ? 4u : 0u, is_write, P.txn + at, room);
-      } else {                                         // warp path: staged in the pool
-        const uint4 *src = reinterpret_cast<const uint4 *>(stage + slot);
-        uint4 *dst = reinterpret_cast<uint4 *>(P.txn + at);
-        for (uint32_t k = sub; k < room; k += 4) { dst[2 * k] = src[2 * k]; dst[2 * k + 1] = src[2 * k + 1]; }
+      } else {                                         // warp path: staged in the pool, in 16 B units
+        const uint4 *src = reinterpret_cast<const uint4 *>(stage) + (slot & 0x3fffu);
+        if (slot & 0x4000u) {                            // compact form: one unit per transaction
+          for (uint32_t k = sub; k < room; k += 4) txn_store(P.txn + at + k, txn_unpack_run(src[k]));
+        } else {
+          uint4 *dst = reinterpret_cast<uint4 *>(P.txn + at);
+          for (uint32_t k = sub; k < room; k += 4) { dst[2 * k] = src[2 * k]; dst[2 * k + 1] = src[2 * k + 1]; }
+        }
       }
     }
     TI_STAMP(13);  // F: offsets, record patch, transactions
@@ -615,13 +619,21 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
           } else if (space != SPACE_LOCAL) fl |= TI_EF_UNDEF_SPACE;
         }
         if (fl) n_txn = 0;                              // fl is warp-uniform here
+        // The pool is handed out in 16 B units.  When every transaction of the instruction is one run of bytes they are
+        // staged in the compact form (one unit each, ti_mem.cuh), else as finished 32 B records (two units each).
+        unsigned rp0[2] = {0, 0}, rlen[2] = {0, 0};
+        bool runs = true;
+        if (pos[0] < n_txn) runs = txn_is_run(t2[0], rp0[0], rlen[0]);
+        if (pos[1] < n_txn) runs = txn_is_run(t2[1], rp0[1], rlen[1]) && runs;
+        const bool compact_form = __all_sync(kFull, runs) && n_txn != 0;
+        const uint32_t n_units = compact_form ? n_txn : 2 * n_txn;
         uint32_t slot = 0;
         if (lane == 0) {
           note_error(ms, fl, rp->opc_off);
           rp->pack_c = (uint8_t)pack_c; rp->cycles = (uint8_t)cycles;
-          slot = n_txn ? atomicAdd(&ms->stage_used, n_txn) : 0;
-          if (slot + n_txn > stage_cap) slot = 0xFFFFu;   // staging full: recomputed when the chunk's transactions leave
-          txn_cnt[item] = (uint8_t)n_txn; txn_slot[item] = (uint16_t)slot;
+          slot = n_txn ? atomicAdd(&ms->stage_used, n_units) : 0;
+          if (slot + n_units > 2 * stage_cap) slot = 0xFFFFu;   // staging full: recomputed when the chunk's transactions leave
+          txn_cnt[item] = (uint8_t)n_txn; txn_slot[item] = (uint16_t)(slot == 0xFFFFu ? 0xFFFFu : slot | (compact_form ? 0x4000u : 0u));
           // the counters this instruction was left out of in W (its space is final only now)
           const unsigned act = __popc(mask);
           if ((op == OP_LOAD || op == OP_STORE || op == OP_MEMBAR || op == OP_TLOAD || op == OP_TSTORE) && act)
@@ -631,8 +643,14 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
         slot = __shfl_sync(kFull, slot, 0);
         if (slot != 0xFFFFu) {
           const unsigned type = is_write ? 4u : 0u;       // GLOBAL_ACC_W / GLOBAL_ACC_R
-          if (pos[0] < n_txn) txn_store(stage + slot + pos[0], reduce_and_send(t2[0], seg, type, is_write));
-          if (pos[1] < n_txn) txn_store(stage + slot + pos[1], reduce_and_send(t2[1], seg, type, is_write));
+          uint4 *unit = reinterpret_cast<uint4 *>(stage) + slot;
+          if (compact_form) {
+            if (pos[0] < n_txn) unit[pos[0]] = txn_pack_run(t2[0], rp0[0], rlen[0], seg, is_write);
+            if (pos[1] < n_txn) unit[pos[1]] = txn_pack_run(t2[1], rp0[1], rlen[1], seg, is_write);
+          } else {
+            if (pos[0] < n_txn) txn_store(reinterpret_cast<ti_txn_rec *>(unit + 2 * pos[0]), reduce_and_send(t2[0], seg, type, is_write));
+            if (pos[1] < n_txn) txn_store(reinterpret_cast<ti_txn_rec *>(unit + 2 * pos[1]), reduce_and_send(t2[1], seg, type, is_write));
+          }
         }
       }
       __syncthreads();
@@ -726,9 +744,9 @@ __global__ void __launch_bounds__(kThreads, TI_MIN_BLOCKS) ti_decode_kernel(cons
 
     // ---------------------------------------------------------------- F: parked for the next iteration
     // (a chunk whose transactions overflowed the staging area included: what was spilled is coalesced again there)
-    if (stage_used > stage_cap && tid == 0) atomicAdd(&P.g->rare[0], 1u);
+    if (stage_used > 2 * stage_cap && tid == 0) atomicAdd(&P.g->rare[0], 1u);    // (stage_used counts 16 B units)
     pend = true; pend_chunk = chunk; pend_par = par; pend_n_mem = n_mem; pend_n_txn = n_txn_chunk;
-    pend_base_inst = base_inst; pend_have_mem = n_warp_path != 0; pend_base_mem = base_mem; pend_recompute = stage_used > stage_cap;
+    pend_base_inst = base_inst; pend_have_mem = n_warp_path != 0; pend_base_mem = base_mem; pend_recompute = stage_used > 2 * stage_cap;
     TI_STAMP(10);
     if (++done_chunks % kFlushEvery == 0) { __syncthreads(); flush_counters(cnt, P.counters); }
   }

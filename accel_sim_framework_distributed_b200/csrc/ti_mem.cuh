@@ -86,6 +86,41 @@ TI_D void txn_store(ti_txn_rec *dst, const TxnWords &w) {
   d[0] = w.a; d[1] = w.b;
 }
 
+// ---- compact staging form (16 B instead of 32): a transaction whose bytes are ONE run [p0, p0 + len) of its
+// 128 B line -- every access of a lane on its own, and most merged ones -- is kept as block | lanes | run, and
+// becomes a ti_txn_rec only when the chunk's transactions leave shared memory.
+TI_D void run_bytes(unsigned p0, unsigned len, uint32_t (&bytes)[4], uint32_t &chunks) {
+  const unsigned p1 = p0 + len;
+  chunks = 0;
+#pragma unroll
+  for (unsigned w = 0; w < 4; ++w) {
+    const unsigned a = p0 > 32 * w ? p0 : 32 * w, b = p1 < 32 * w + 32 ? p1 : 32 * w + 32;
+    const bool hit = b > a;
+    bytes[w] = hit ? ((b - a == 32 ? 0xffffffffu : ((1u << (b - a)) - 1)) << (a - 32 * w)) : 0u;
+    chunks |= hit ? 1u << w : 0u;
+  }
+}
+TI_D bool txn_is_run(const Txn &t, unsigned &p0, unsigned &len) {
+  len = __popc(t.bytes[0]) + __popc(t.bytes[1]) + __popc(t.bytes[2]) + __popc(t.bytes[3]);
+  p0 = t.bytes[0] ? __ffs(t.bytes[0]) - 1 : t.bytes[1] ? 31 + __ffs(t.bytes[1]) : t.bytes[2] ? 63 + __ffs(t.bytes[2]) : 95 + __ffs(t.bytes[3]);
+  if (!len) return false;
+  uint32_t b[4], c;
+  run_bytes(p0, len, b, c);
+  return b[0] == t.bytes[0] && b[1] == t.bytes[1] && b[2] == t.bytes[2] && b[3] == t.bytes[3] && c == t.chunks;
+}
+TI_D uint4 txn_pack_run(const Txn &t, unsigned p0, unsigned len, unsigned seg, unsigned is_write) {
+  return make_uint4((uint32_t)t.block, (uint32_t)(t.block >> 32), t.lanes,
+                    p0 | (len - 1) << 7 | (seg == 128 ? 2u : seg == 64 ? 1u : 0u) << 14 | is_write << 16);
+}
+TI_D TxnWords txn_unpack_run(const uint4 c) {
+  Txn x;
+  x.block = (uint64_t)c.y << 32 | c.x;
+  x.lanes = c.z;
+  run_bytes(c.w & 127, (c.w >> 7 & 127) + 1, x.bytes, x.chunks);
+  const unsigned is_write = c.w >> 16 & 1;
+  return reduce_and_send(x, 32u << (c.w >> 14 & 3), is_write ? 4u : 0u, is_write);
+}
+
 // ---- address decompression.  `q` = smem offset of the first token after the mode field, `le` =
 // offset of the line's '\n'; tokpos = 33 u16 of per-warp scratch.  Returns this lane's address.
 TI_D_COLD uint64_t decode_addresses(const uint8_t *text, const uint32_t *dlmap32, unsigned q, unsigned le, unsigned mode, uint32_t mask,
