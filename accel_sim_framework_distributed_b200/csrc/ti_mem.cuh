@@ -477,10 +477,16 @@ TI_D_COLD unsigned coalesce_global(const DecodeParams &P, uint32_t mask, uint64_
     // every leader's block goes through the warp's scratch once: a broadcast LDS.64 per leader instead
     // of two shuffles (a divergent access has 32 leaders)
     uint64_t *ks = reinterpret_cast<uint64_t *>(scratch);
+    const bool many = !mB && __popc(LA) > 12;            // warp-uniform
     __syncwarp();
-    ks[lane] = keyA;
+    ks[lane] = (many && !leadA) ? ~0ull : keyA;          // (all ones is no block address: never below a key)
     __syncwarp();
-    if (!mB) {                                           // warp-uniform: nobody straddles, only A ranks are needed
+    if (many) {
+      // a divergent access (up to 32 leaders): all 32 slots, two per 128-bit broadcast load, no loop over a mask
+      const ulonglong2 *k2 = reinterpret_cast<const ulonglong2 *>(ks);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) { const ulonglong2 v = k2[i]; cntA += (v.x < keyA) + (v.y < keyA); }
+    } else if (!mB) {                                    // warp-uniform: nobody straddles, only A ranks are needed
       for (uint32_t m = LA; m; m &= m - 1) cntA += ks[__ffs(m) - 1] < keyA;
     } else {
       for (uint32_t m = LA; m; m &= m - 1) {
